@@ -1,0 +1,550 @@
+// fb_api.cu -- C ABI of libfairify_b200.so (declared in include/fairify_b200.h) and the runtime-shape
+// kernel launchers.  No torch types; device pointers, sizes and a cudaStream_t (as void*) only.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/fairify_b200.h"
+#include "fb_generic.cuh"
+#include "fb_registry.h"
+#include "fb_spec_ops.cuh"
+
+static_assert(sizeof(fb_prune_out) == sizeof(FbPruneOut), "fb_prune_out and FbPruneOut must match");
+
+// ---------------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------------
+static thread_local char fb_err[512] = "";
+
+static int fb_fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(fb_err, sizeof(fb_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define FB_CUDA(expr)                                                                                      \
+    do {                                                                                                   \
+        cudaError_t e_ = (expr);                                                                           \
+        if (e_ != cudaSuccess)                                                                             \
+            return fb_fail(FB_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char *fb_last_error(void) { return fb_err; }
+extern "C" int fb_version(void) { return 100; }
+
+extern "C" int fb_num_sms(int *out)
+{
+    int dev = 0, sms = 0;
+    FB_CUDA(cudaGetDevice(&dev));
+    FB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    *out = sms;
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// model
+// ---------------------------------------------------------------------------------------------------
+struct fb_model {
+    int device = 0, num_sms = 0;
+    GenNet gen{};
+    std::vector<double> hW64, hB64;
+    std::vector<float> hW32, hB32;
+    double *dW64 = nullptr, *dB64 = nullptr;
+    float *dW32 = nullptr, *dB32 = nullptr;
+    const FbSpecEntry *spec = nullptr;
+    void *p64 = nullptr, *p32 = nullptr;
+};
+
+static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
+{
+    const FbSpecTable *tables[] = {&fb_spec_table_a, &fb_spec_table_b, &fb_spec_table_c, &fb_spec_table_d,
+                                   &fb_spec_table_e};
+    for (const FbSpecTable *t : tables)
+        for (int k = 0; k < t->count; ++k) {
+            const FbSpecEntry &e = t->entries[k];
+            if (e.nd != L + 1) continue;
+            bool same = true;
+            for (int i = 0; i <= L; ++i) same = same && (e.dims[i] == dims[i]);
+            if (same) return &e;
+        }
+    return nullptr;
+}
+
+extern "C" void fb_model_destroy(fb_model *m)
+{
+    if (!m) return;
+    if (m->spec) m->spec->free_params(m->p64, m->p32);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32);
+    delete m;
+}
+
+extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const float *b, fb_model **out)
+{
+    if (!dims || !w || !b || !out) return fb_fail(FB_ERR_INVALID, "fb_model_create: null argument");
+    if (L < 1 || L > FB_MAX_LAYERS) return fb_fail(FB_ERR_UNSUPPORTED, "fb_model_create: %d layers (supported: 1..%d)", L, FB_MAX_LAYERS);
+    if (dims[L] != 1) return fb_fail(FB_ERR_UNSUPPORTED, "fb_model_create: output width %d (the path is defined for a single logit)", dims[L]);
+    fb_model *m = new (std::nothrow) fb_model;
+    if (!m) return fb_fail(FB_ERR_NOMEM, "fb_model_create: out of host memory");
+    GenNet &g = m->gen;
+    g.L = L; g.maxw = dims[0];
+    int wo = 0, bo = 0;
+    for (int l = 0; l <= L; ++l) {
+        if (dims[l] < 1 || dims[l] > FB_MAXW) { delete m; return fb_fail(FB_ERR_UNSUPPORTED, "fb_model_create: layer width %d (supported: 1..%d)", dims[l], FB_MAXW); }
+        g.dims[l] = dims[l];
+        if (dims[l] > g.maxw) g.maxw = dims[l];
+    }
+    for (int l = 0; l < L; ++l) { g.woff[l] = wo; g.boff[l] = bo; wo += dims[l] * dims[l + 1]; bo += dims[l + 1]; }
+    g.woff[L] = wo; g.boff[L] = bo; g.P = wo; g.N = bo;
+    if ((g.N + 31) / 32 > FB_MAX_NW) { delete m; return fb_fail(FB_ERR_UNSUPPORTED, "fb_model_create: %d neurons (supported: <= %d)", g.N, FB_MAX_NW * 32); }
+    m->hW32.assign(w, w + g.P); m->hB32.assign(b, b + g.N);
+    m->hW64.resize(g.P); m->hB64.resize(g.N);
+    for (int k = 0; k < g.P; ++k) {
+        if (!std::isfinite(w[k])) { delete m; return fb_fail(FB_ERR_INVALID, "fb_model_create: weight %d is not finite", k); }
+        // -0.0 -> +0.0: the reference's `weight < 0` test treats both as non-negative and the products are
+        // zero either way, so results are unchanged while the device can test the sign bit alone
+        m->hW32[k] = (w[k] == 0.0f) ? 0.0f : w[k];
+        m->hW64[k] = (double)m->hW32[k];
+    }
+    for (int k = 0; k < g.N; ++k) {
+        if (!std::isfinite(b[k])) { delete m; return fb_fail(FB_ERR_INVALID, "fb_model_create: bias %d is not finite", k); }
+        m->hB64[k] = (double)b[k];
+    }
+    cudaError_t e = cudaGetDevice(&m->device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&m->num_sms, cudaDevAttrMultiProcessorCount, m->device);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dW64, sizeof(double) * g.P);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dB64, sizeof(double) * g.N);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dW32, sizeof(float) * g.P);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dB32, sizeof(float) * g.N);
+    if (e == cudaSuccess) e = cudaMemcpy(m->dW64, m->hW64.data(), sizeof(double) * g.P, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(m->dB64, m->hB64.data(), sizeof(double) * g.N, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(m->dW32, m->hW32.data(), sizeof(float) * g.P, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(m->dB32, m->hB32.data(), sizeof(float) * g.N, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        fb_model_destroy(m);
+        return fb_fail(FB_ERR_CUDA, "fb_model_create: %s (is a CUDA device available? there is no CPU path)", cudaGetErrorString(e));
+    }
+    g.W64 = m->dW64; g.B64 = m->dB64; g.W32 = m->dW32; g.B32 = m->dB32;
+    m->spec = fb_find_spec(L, dims);
+    if (m->spec) {
+        m->p64 = m->spec->make_params64(m->hW64.data(), m->hB64.data());
+        m->p32 = m->spec->make_params32(m->hW32.data(), m->hB32.data());
+        if (!m->p64 || !m->p32) { fb_model_destroy(m); return fb_fail(FB_ERR_NOMEM, "fb_model_create: out of host memory"); }
+    }
+    *out = m;
+    return FB_OK;
+}
+
+extern "C" int fb_model_info(const fb_model *m, int *L, int *N, int *P, int *specialised)
+{
+    if (!m) return fb_fail(FB_ERR_INVALID, "fb_model_info: null model");
+    if (L) *L = m->gen.L;
+    if (N) *N = m->gen.N;
+    if (P) *P = m->gen.P;
+    if (specialised) *specialised = m->spec ? 1 : 0;
+    return FB_OK;
+}
+
+// set FAIRIFY_B200_FORCE_GENERIC=1 to route every model through the runtime-shape kernels (tests)
+static bool fb_use_spec(const fb_model *m)
+{
+    static const bool force_generic = [] { const char *v = getenv("FAIRIFY_B200_FORCE_GENERIC"); return v && v[0] == '1'; }();
+    return m->spec != nullptr && !force_generic;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// partition grid
+// ---------------------------------------------------------------------------------------------------
+#define FB_MAX_D 64
+struct FbGridDesc {
+    int d;
+    int col[FB_MAX_D];          // column of the k-th key (digit order: last key fastest)
+    int64_t lo[FB_MAX_D], hi[FB_MAX_D], nch[FB_MAX_D];   // by column
+    int64_t T;
+};
+struct fb_grid { FbGridDesc g; int64_t n; };
+
+__global__ void __launch_bounds__(256)
+fb_grid_boxes_kernel(const FbGridDesc g, int64_t first, int64_t count, int32_t *__restrict__ boxes)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < count; p += stride) {
+        int64_t idx = first + p;
+        int2 *box = reinterpret_cast<int2 *>(boxes + p * (2 * g.d));
+        for (int k = g.d - 1; k >= 0; --k) {
+            const int c = g.col[k];
+            const int64_t nc = g.nch[c];
+            int64_t a = g.lo[c], b = g.hi[c];
+            if (nc > 1) {
+                const int64_t digit = idx % nc;
+                idx /= nc;
+                a = g.lo[c] + digit * g.T;
+                b = min(a + g.T - 1, g.hi[c]);
+            }
+            box[c] = make_int2((int)a, (int)b);
+        }
+    }
+}
+
+extern "C" int fb_grid_create(int d, const int64_t *lo, const int64_t *hi, int64_t T, const int32_t *key_order, fb_grid **out)
+{
+    if (!lo || !hi || !key_order || !out) return fb_fail(FB_ERR_INVALID, "fb_grid_create: null argument");
+    if (d < 1 || d > FB_MAX_D) return fb_fail(FB_ERR_UNSUPPORTED, "fb_grid_create: %d features (supported: 1..%d)", d, FB_MAX_D);
+    if (T < 1) return fb_fail(FB_ERR_INVALID, "fb_grid_create: partition size %lld", (long long)T);
+    fb_grid *g = new (std::nothrow) fb_grid;
+    if (!g) return fb_fail(FB_ERR_NOMEM, "fb_grid_create: out of host memory");
+    g->g.d = d; g->g.T = T; g->n = 1;
+    std::vector<int> seen(d, 0);
+    for (int k = 0; k < d; ++k) {
+        const int c = key_order[k];
+        if (c < 0 || c >= d || seen[c]) { delete g; return fb_fail(FB_ERR_INVALID, "fb_grid_create: key_order is not a permutation"); }
+        seen[c] = 1; g->g.col[k] = c;
+    }
+    for (int c = 0; c < d; ++c) {
+        if (hi[c] < lo[c] || lo[c] < INT32_MIN || hi[c] > INT32_MAX) { delete g; return fb_fail(FB_ERR_INVALID, "fb_grid_create: bad range for column %d", c); }
+        const int64_t size = hi[c] - lo[c] + 1;
+        g->g.lo[c] = lo[c]; g->g.hi[c] = hi[c];
+        g->g.nch[c] = (size <= T) ? 1 : (size + T - 1) / T;     // utils/input_partition.py:24-27
+        if (g->n > INT64_MAX / g->g.nch[c]) { delete g; return fb_fail(FB_ERR_UNSUPPORTED, "fb_grid_create: grid size overflows int64"); }
+        g->n *= g->g.nch[c];
+    }
+    *out = g;
+    return FB_OK;
+}
+extern "C" void fb_grid_destroy(fb_grid *g) { delete g; }
+extern "C" int64_t fb_grid_size(const fb_grid *g) { return g ? g->n : -1; }
+
+extern "C" int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int32_t *boxes, void *stream)
+{
+    if (!g || !boxes) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: null argument");
+    if (first < 0 || count < 0 || first + count > g->n) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: range [%lld, %lld) outside the grid of %lld", (long long)first, (long long)(first + count), (long long)g->n);
+    if (count == 0) return FB_OK;
+    int sms = 0;
+    if (fb_num_sms(&sms)) return FB_ERR_CUDA;
+    const int grid = (int)std::min<int64_t>((count + 255) / 256, (int64_t)sms * 8);
+    fb_grid_boxes_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g->g, first, count, boxes);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// profile
+// ---------------------------------------------------------------------------------------------------
+// Samples are split into `chunks` slices per partition only when there are too few partitions to fill
+// the machine with one warp each.
+static void fb_pick_chunks(const fb_model *m, int64_t n, int S, int *chunks, int *chunk_len)
+{
+    const int max_len = FB_PROFILE_MAX_STEPS * 32;
+    const int64_t want_warps = (int64_t)m->num_sms * 64;
+    int c = 1;
+    if (n < want_warps) c = (int)std::min<int64_t>((S + 31) / 32, (want_warps + n - 1) / n);
+    c = std::max(c, (S + max_len - 1) / max_len);
+    int len = (S + c - 1) / c;
+    len = ((len + 31) / 32) * 32;
+    c = (S + len - 1) / len;
+    *chunks = std::max(c, 1); *chunk_len = len;
+}
+
+static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const void *boxes, int S, bool need_s)
+{
+    if (!m) return fb_fail(FB_ERR_INVALID, "%s: null model", fn);
+    if (n < 0) return fb_fail(FB_ERR_INVALID, "%s: n = %lld", fn, (long long)n);
+    if (n > 0 && !boxes) return fb_fail(FB_ERR_INVALID, "%s: null boxes", fn);
+    if (need_s && (S < 1 || S > 65535)) return fb_fail(FB_ERR_INVALID, "%s: S = %d (supported: 1..65535)", fn, S);
+    return FB_OK;
+}
+
+static size_t fb_profile_gen_smem(const fb_model *m)
+{
+    return sizeof(double) * ((size_t)m->gen.P + m->gen.N) + sizeof(uint32_t) * (FB_PROFILE_THREADS / 32) * m->gen.N;
+}
+
+extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                          int64_t first_index, uint32_t *counts, void *stream)
+{
+    if (int rc = fb_check_batch("fb_profile", m, n, boxes, S, true)) return rc;
+    if (n == 0) return FB_OK;
+    if (!counts) return fb_fail(FB_ERR_INVALID, "fb_profile: null counts");
+    cudaStream_t st = (cudaStream_t)stream;
+    int chunks, chunk_len;
+    fb_pick_chunks(m, n, S, &chunks, &chunk_len);
+    if (chunks > 1) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));
+    if (fb_use_spec(m)) {
+        FB_CUDA(m->spec->profile(m->p64, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks, chunk_len,
+                                 counts, m->num_sms, st));
+        return FB_OK;
+    }
+    const size_t smem = fb_profile_gen_smem(m);
+    if (smem > 227 * 1024) return fb_fail(FB_ERR_UNSUPPORTED, "fb_profile: model needs %zu bytes of shared memory", smem);
+    const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
+    if (samples == nullptr) {
+        auto k = fb_profile_gen_kernel<true>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_PROFILE_THREADS, smem, ctas, m->num_sms), FB_PROFILE_THREADS, smem, st>>>(
+            m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts);
+    } else {
+        auto k = fb_profile_gen_kernel<false>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_PROFILE_THREADS, smem, ctas, m->num_sms), FB_PROFILE_THREADS, smem, st>>>(
+            m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts);
+    }
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// interval bounds + masks
+// ---------------------------------------------------------------------------------------------------
+extern "C" int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const uint32_t *counts, const double *tol,
+                      const fb_prune_out *out, void *stream)
+{
+    if (int rc = fb_check_batch("fb_ibp", m, n, boxes, 1, false)) return rc;
+    if (!out) return fb_fail(FB_ERR_INVALID, "fb_ibp: null output block");
+    if (n == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const FbPruneOut *o = reinterpret_cast<const FbPruneOut *>(out);
+    if (fb_use_spec(m)) {
+        FB_CUDA(m->spec->ibp(m->p64, n, boxes, counts, tol, o, m->num_sms, st));
+        return FB_OK;
+    }
+    auto k = fb_ibp_gen_kernel;
+    const int64_t ctas = (n + FB_IBP_GEN_WARPS - 1) / FB_IBP_GEN_WARPS;
+    k<<<fb_grid_for(k, FB_IBP_GEN_WARPS * 32, 0, ctas, m->num_sms), FB_IBP_GEN_WARPS * 32, 0, st>>>(m->gen, n, boxes, counts,
+                                                                                                   tol, *o);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+extern "C" int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                        int64_t first_index, const double *tol, const fb_prune_out *out, void *stream)
+{
+    if (int rc = fb_check_batch("fb_prune", m, n, boxes, S, true)) return rc;
+    if (!out) return fb_fail(FB_ERR_INVALID, "fb_prune: null output block");
+    if (n == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t *counts = nullptr;
+    FB_CUDA(cudaMallocAsync(&counts, sizeof(uint32_t) * n * m->gen.N, st));
+    int rc = fb_profile(m, n, boxes, samples, S, seed, first_index, counts, stream);
+    if (rc == FB_OK) rc = fb_ibp(m, n, boxes, counts, tol, out, stream);
+    cudaFreeAsync(counts, st);
+    return rc;
+}
+
+// host-buffer variant ------------------------------------------------------------------------------
+namespace {
+struct DevBuf {
+    void *p = nullptr;
+    cudaStream_t st;
+    explicit DevBuf(cudaStream_t s) : st(s) {}
+    ~DevBuf() { if (p) cudaFreeAsync(p, st); }
+    cudaError_t alloc(size_t bytes) { return cudaMallocAsync(&p, bytes ? bytes : 1, st); }
+};
+}  // namespace
+
+extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                             uint64_t seed, int64_t first_index, const double *tol, const fb_prune_out *out, void *stream)
+{
+    if (int rc = fb_check_batch("fb_prune_host", m, n, boxes, S, true)) return rc;
+    if (!out) return fb_fail(FB_ERR_INVALID, "fb_prune_host: null output block");
+    if (n == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = m->gen.N, NW = (N + 31) / 32, d = m->gen.dims[0];
+    DevBuf dboxes(st), dsamp(st), dtol(st);
+    FB_CUDA(dboxes.alloc(sizeof(int32_t) * n * d * 2));
+    FB_CUDA(cudaMemcpyAsync(dboxes.p, boxes, sizeof(int32_t) * n * d * 2, cudaMemcpyHostToDevice, st));
+    if (samples) {
+        FB_CUDA(dsamp.alloc(sizeof(int32_t) * n * S * d));
+        FB_CUDA(cudaMemcpyAsync(dsamp.p, samples, sizeof(int32_t) * n * S * d, cudaMemcpyHostToDevice, st));
+    }
+    if (tol) {
+        FB_CUDA(dtol.alloc(sizeof(double) * N));
+        FB_CUDA(cudaMemcpyAsync(dtol.p, tol, sizeof(double) * N, cudaMemcpyHostToDevice, st));
+    }
+    // one device buffer per requested output
+    struct Slot { void *host; size_t bytes; void **dev_field; };
+    fb_prune_out dev{};
+    const size_t mb = sizeof(uint32_t) * n * NW, fb = sizeof(double) * n * N;
+    Slot slots[] = {
+        {out->cand, mb, (void **)&dev.cand},     {out->b_dead, mb, (void **)&dev.b_dead},
+        {out->dead, mb, (void **)&dev.dead},     {out->sliver, mb, (void **)&dev.sliver},
+        {out->verdict, (size_t)n, (void **)&dev.verdict}, {out->counts, sizeof(uint16_t) * n * N, (void **)&dev.counts},
+        {out->ws_lb, fb, (void **)&dev.ws_lb},   {out->ws_ub, fb, (void **)&dev.ws_ub},
+        {out->pl_lb, fb, (void **)&dev.pl_lb},   {out->pl_ub, fb, (void **)&dev.pl_ub},
+        {out->lb_rd, fb, (void **)&dev.lb_rd},   {out->ub_ru, fb, (void **)&dev.ub_ru},
+    };
+    std::vector<DevBuf> bufs;
+    bufs.reserve(sizeof(slots) / sizeof(slots[0]));
+    for (Slot &s : slots) {
+        if (!s.host) continue;
+        bufs.emplace_back(st);
+        FB_CUDA(bufs.back().alloc(s.bytes));
+        *s.dev_field = bufs.back().p;
+    }
+    int rc = fb_prune(m, n, (const int32_t *)dboxes.p, (const int32_t *)dsamp.p, S, seed, first_index,
+                      (const double *)dtol.p, &dev, stream);
+    if (rc != FB_OK) return rc;
+    for (Slot &s : slots)
+        if (s.host) FB_CUDA(cudaMemcpyAsync(s.host, *s.dev_field, s.bytes, cudaMemcpyDeviceToHost, st));
+    FB_CUDA(cudaStreamSynchronize(st));
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// logits, pair screen, partition screen
+// ---------------------------------------------------------------------------------------------------
+extern "C" int fb_forward_f64(const fb_model *m, int64_t rows, const double *X, const uint32_t *dead_bits, double *logits,
+                              void *stream)
+{
+    if (!m || rows < 0 || (rows > 0 && (!X || !logits))) return fb_fail(FB_ERR_INVALID, "fb_forward_f64: bad argument");
+    if (rows == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fb_use_spec(m)) { FB_CUDA(m->spec->forward64(m->p64, rows, X, dead_bits, logits, m->num_sms, st)); return FB_OK; }
+    auto k = fb_forward_gen_kernel<double>;
+    const int64_t ctas = (rows + FB_FWD_THREADS - 1) / FB_FWD_THREADS;
+    k<<<fb_grid_for(k, FB_FWD_THREADS, 0, ctas, m->num_sms), FB_FWD_THREADS, 0, st>>>(m->gen, rows, X, dead_bits, logits);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+extern "C" int fb_forward_f32(const fb_model *m, int64_t rows, const float *X, const uint32_t *dead_bits, float *logits,
+                              void *stream)
+{
+    if (!m || rows < 0 || (rows > 0 && (!X || !logits))) return fb_fail(FB_ERR_INVALID, "fb_forward_f32: bad argument");
+    if (rows == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fb_use_spec(m)) { FB_CUDA(m->spec->forward32(m->p32, rows, X, dead_bits, logits, m->num_sms, st)); return FB_OK; }
+    auto k = fb_forward_gen_kernel<float>;
+    const int64_t ctas = (rows + FB_FWD_THREADS - 1) / FB_FWD_THREADS;
+    k<<<fb_grid_for(k, FB_FWD_THREADS, 0, ctas, m->num_sms), FB_FWD_THREADS, 0, st>>>(m->gen, rows, X, dead_bits, logits);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+extern "C" int fb_pair_screen(const fb_model *m, int64_t rows, const float *X, int n_pa, const int32_t *pa_cols_host,
+                              int k_alts, const float *alts, uint8_t *orig_pred, int32_t *first_flip, void *stream)
+{
+    if (!m || rows < 0 || !pa_cols_host || (rows > 0 && (!X || !orig_pred || !first_flip)))
+        return fb_fail(FB_ERR_INVALID, "fb_pair_screen: bad argument");
+    if (n_pa < 1 || n_pa > FB_MAX_PA) return fb_fail(FB_ERR_UNSUPPORTED, "fb_pair_screen: %d protected columns (supported: 1..%d)", n_pa, FB_MAX_PA);
+    if (k_alts < 0 || (k_alts > 0 && !alts)) return fb_fail(FB_ERR_INVALID, "fb_pair_screen: bad alternatives");
+    FbPaCols pa{};
+    pa.n = n_pa;
+    for (int q = 0; q < n_pa; ++q) {
+        if (pa_cols_host[q] < 0 || pa_cols_host[q] >= m->gen.dims[0]) return fb_fail(FB_ERR_INVALID, "fb_pair_screen: protected column %d out of range", pa_cols_host[q]);
+        pa.col[q] = pa_cols_host[q];
+    }
+    if (rows == 0) return FB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fb_use_spec(m)) {
+        FB_CUDA(m->spec->pair_screen(m->p32, rows, X, &pa, k_alts, alts, orig_pred, first_flip, m->num_sms, st));
+        return FB_OK;
+    }
+    auto k = fb_pair_screen_gen_kernel;
+    const int64_t ctas = (rows + FB_FWD_THREADS - 1) / FB_FWD_THREADS;
+    k<<<fb_grid_for(k, FB_FWD_THREADS, 0, ctas, m->num_sms), FB_FWD_THREADS, 0, st>>>(m->gen, rows, X, pa, k_alts, alts,
+                                                                                 orig_pred, first_flip);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+__global__ void __launch_bounds__(256)
+fb_ce_unpack_kernel(int64_t n, int d, int pa_col, const int32_t *__restrict__ boxes,
+                    const unsigned long long *__restrict__ key, int32_t *__restrict__ ce_sample,
+                    int32_t *__restrict__ pa_pos, int32_t *__restrict__ pa_neg, uint8_t *__restrict__ verdict)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        const unsigned long long k = key[p];
+        if (k == ~0ull) { ce_sample[p] = -1; pa_pos[p] = -1; pa_neg[p] = -1; continue; }
+        const int lo = boxes[p * (2 * d) + 2 * pa_col];
+        ce_sample[p] = (int32_t)(k >> 32);
+        pa_pos[p] = lo + (int32_t)((k >> 16) & 0xffffu);
+        pa_neg[p] = lo + (int32_t)(k & 0xffffu);
+        if (verdict) verdict[p] |= FB_VERDICT_CE;
+    }
+}
+
+extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                   uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
+                                   int32_t *pa_neg, uint8_t *verdict, void *stream)
+{
+    if (int rc = fb_check_batch("fb_partition_screen", m, n, boxes, S, true)) return rc;
+    if (pa_col < 0 || pa_col >= m->gen.dims[0]) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: protected column %d out of range", pa_col);
+    if (n == 0) return FB_OK;
+    if (!ce_sample || !pa_pos || !pa_neg) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: null output");
+    cudaStream_t st = (cudaStream_t)stream;
+    int chunks, chunk_len;
+    fb_pick_chunks(m, n, S, &chunks, &chunk_len);
+    DevBuf key(st);
+    FB_CUDA(key.alloc(sizeof(unsigned long long) * n));
+    FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
+    if (fb_use_spec(m)) {
+        FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
+                                          chunk_len, pa_col, (unsigned long long *)key.p, m->num_sms, st));
+    } else {
+        const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
+        if (samples == nullptr) {
+            auto k = fb_partition_screen_gen_kernel<true>;
+            k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, m->num_sms), FB_PROFILE_THREADS, 0, st>>>(
+                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, (unsigned long long *)key.p);
+        } else {
+            auto k = fb_partition_screen_gen_kernel<false>;
+            k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, m->num_sms), FB_PROFILE_THREADS, 0, st>>>(
+                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, (unsigned long long *)key.p);
+        }
+        FB_CUDA(cudaGetLastError());
+    }
+    const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)m->num_sms * 8);
+    fb_ce_unpack_kernel<<<grid, 256, 0, st>>>(n, m->gen.dims[0], pa_col, boxes, (const unsigned long long *)key.p,
+                                              ce_sample, pa_pos, pa_neg, verdict);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// FP64 issue-rate microbenchmark: 8 independent DFMA chains per thread, enough warps to saturate the
+// pipe.  Gives the measured denominator for "% of FP64 peak".
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) fb_dfma_kernel(int iters, double seed, double *sink)
+{
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            a0 = __fma_rn(a0, m, c); a1 = __fma_rn(a1, m, c); a2 = __fma_rn(a2, m, c); a3 = __fma_rn(a3, m, c);
+            a4 = __fma_rn(a4, m, c); a5 = __fma_rn(a5, m, c); a6 = __fma_rn(a6, m, c); a7 = __fma_rn(a7, m, c);
+        }
+    }
+    const double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == 12345.678) sink[0] = s;       // never true; keeps the chains alive
+}
+
+extern "C" int fb_fp64_peak(int iters, double *tflops, double *ms_out)
+{
+    if (iters < 1 || !tflops) return fb_fail(FB_ERR_INVALID, "fb_fp64_peak: bad argument");
+    int sms = 0;
+    if (fb_num_sms(&sms)) return FB_ERR_CUDA;
+    double *sink = nullptr;
+    FB_CUDA(cudaMalloc(&sink, sizeof(double)));
+    cudaEvent_t e0, e1;
+    FB_CUDA(cudaEventCreate(&e0)); FB_CUDA(cudaEventCreate(&e1));
+    const int grid = sms * 8;
+    fb_dfma_kernel<<<grid, 256>>>(iters / 8 + 1, 1.0, sink);           // warm-up
+    FB_CUDA(cudaEventRecord(e0));
+    fb_dfma_kernel<<<grid, 256>>>(iters, 1.0, sink);
+    FB_CUDA(cudaEventRecord(e1));
+    FB_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    FB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    const double flops = (double)grid * 256.0 * (double)iters * 16.0 * 8.0 * 2.0;
+    *tflops = flops / (ms * 1e-3) / 1e12;
+    if (ms_out) *ms_out = ms;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    return FB_OK;
+}

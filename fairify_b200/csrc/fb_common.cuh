@@ -1,0 +1,96 @@
+// fb_common.cuh -- shared device helpers of the fairify_b200 pre-solver kernels (sm_100a).
+//
+// Network description comes in two flavours:
+//   * Spec<D0, D1, ..., 1>: layer widths are template constants.  Weights travel as a __grid_constant__
+//     kernel parameter, so every weight is a constant-bank operand of its DFMA/DMUL (no load
+//     instruction at all) and activations / bounds live in registers.  Used for every architecture in
+//     FB_SPEC_LIST (all reference models with at most ~2100 weights).
+//   * GenNet: runtime widths, weights in global memory (staged to shared memory where a kernel reuses
+//     them), activations in local arrays.  Covers everything else (AC-4/5/7, BM-4/7/8, GC-5, unknown nets).
+// Both implement exactly the arithmetic of oracle/fairify_oracle.c: term order i ascending, one fused
+// multiply-add per term in the forward passes, separately rounded product and sum in the interval
+// recurrence, bias added last.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define FB_MAX_LAYERS 16
+#define FB_MAXW 160            // widest layer the generic path supports (reference max: 150, BM-4)
+#define FB_MAX_NW 32           // mask words per partition (N <= 1024 neurons)
+#define FB_WARP 32
+
+// ---------------------------------------------------------------------------------------------------
+// Philox4x32-10, counter = (sample, partition_lo, partition_hi, feature/4), key = (seed_lo, seed_hi).
+// Bit-identical to philox4x32_10() in the oracle.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void fb_philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1, uint32_t (&out)[4])
+{
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// value in [lo, lo+range) from one 32-bit word
+__device__ __forceinline__ int32_t fb_map_range(uint32_t word, int32_t lo, uint32_t range)
+{
+    return lo + (int32_t)__umulhi(word, range);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Compile-time network shape.
+// ---------------------------------------------------------------------------------------------------
+template <int... D>
+struct Spec {
+    static constexpr int NL = (int)sizeof...(D) - 1;     // weight layers
+    static constexpr int ND = (int)sizeof...(D);
+    __host__ __device__ static constexpr int dim(int l) { constexpr int d[ND] = {D...}; return d[l]; }
+    __host__ __device__ static constexpr int woff(int l) { int o = 0; for (int k = 0; k < l; ++k) o += dim(k) * dim(k + 1); return o; }
+    __host__ __device__ static constexpr int boff(int l) { int o = 0; for (int k = 0; k < l; ++k) o += dim(k + 1); return o; }
+    static constexpr int P = woff(NL);
+    static constexpr int N = boff(NL);
+    static constexpr int D0 = dim(0);
+    static constexpr int NW = (N + 31) / 32;              // mask words per partition
+};
+
+template <class S, typename T>
+struct SpecParams {
+    T w[S::P];      // layer-major, each [in][out] row-major (Keras kernel layout)
+    T b[S::N];
+};
+
+// ---------------------------------------------------------------------------------------------------
+// Runtime network shape (generic path).  W64/W32 point at device copies with the same layout as above.
+// ---------------------------------------------------------------------------------------------------
+struct GenNet {
+    int L, N, P, maxw;
+    int dims[FB_MAX_LAYERS + 1];
+    int woff[FB_MAX_LAYERS + 1];
+    int boff[FB_MAX_LAYERS + 1];
+    const double *W64, *B64;
+    const float *W32, *B32;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// small arithmetic helpers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool fb_pos(double v) { return __double_as_longlong(v) > 0; }   // v > 0 (no NaNs here)
+__device__ __forceinline__ bool fb_pos(float v) { return __float_as_int(v) > 0; }
+__device__ __forceinline__ bool fb_nonzero(double v) { return (__double_as_longlong(v) << 1) != 0; }
+__device__ __forceinline__ bool fb_signbit(double v) { return __double2hiint(v) < 0; }
+
+__device__ __forceinline__ double fb_fma(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float fb_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fb_add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float fb_add(float a, float b) { return __fadd_rn(a, b); }
+
+// verdict byte
+#define FB_VERDICT_CERTIFIED 1u     // output logit provably one-signed over the box (outward-rounded enclosure)
+#define FB_VERDICT_CE        2u     // sampled counterexample pair found by the partition screen
+#define FB_VERDICT_SLIVER    4u     // some neuron's bound is within rounding error of 0: host Z3 decides s_dead

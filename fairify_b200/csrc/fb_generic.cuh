@@ -1,0 +1,363 @@
+// fb_generic.cuh -- runtime-shape kernels (see fb_common.cuh).  Same arithmetic, same term order as
+// the specialised kernels and the oracle; used for networks outside FB_SPEC_LIST.
+#pragma once
+#include "fb_common.cuh"
+#include "fb_spec.cuh"   // FbPruneOut, FbPaCols, thread-count macros
+
+// ---------------------------------------------------------------------------------------------------
+// forward pass, one sample per thread, activations in two local arrays, outputs blocked by 4 so one
+// activation load feeds four independent FMA chains.  Visit::neuron(idx, last, pre) -> activation.
+// ---------------------------------------------------------------------------------------------------
+template <typename T, class Visit>
+__device__ __forceinline__ T fb_gen_forward(const GenNet &net, const T *__restrict__ W, const T *__restrict__ B,
+                                            T *in, T *out, Visit &vis)
+{
+    for (int l = 0; l < net.L; ++l) {
+        const int IN = net.dims[l], OUT = net.dims[l + 1];
+        const T *w = W + net.woff[l];
+        const T *b = B + net.boff[l];
+        const bool last = (l == net.L - 1);
+        const int full = OUT & ~3;
+        int j0 = 0;
+        for (; j0 < full; j0 += 4) {
+            T a0 = (T)0, a1 = (T)0, a2 = (T)0, a3 = (T)0;
+            const T *wr = w + j0;
+            for (int i = 0; i < IN; ++i, wr += OUT) {
+                const T xv = in[i];
+                a0 = fb_fma(wr[0], xv, a0); a1 = fb_fma(wr[1], xv, a1);
+                a2 = fb_fma(wr[2], xv, a2); a3 = fb_fma(wr[3], xv, a3);
+            }
+            out[j0 + 0] = vis.neuron(net.boff[l] + j0 + 0, last, fb_add(a0, b[j0 + 0]));
+            out[j0 + 1] = vis.neuron(net.boff[l] + j0 + 1, last, fb_add(a1, b[j0 + 1]));
+            out[j0 + 2] = vis.neuron(net.boff[l] + j0 + 2, last, fb_add(a2, b[j0 + 2]));
+            out[j0 + 3] = vis.neuron(net.boff[l] + j0 + 3, last, fb_add(a3, b[j0 + 3]));
+        }
+        for (; j0 < OUT; ++j0) {
+            T a0 = (T)0;
+            const T *wr = w + j0;
+            for (int i = 0; i < IN; ++i, wr += OUT) a0 = fb_fma(wr[0], in[i], a0);
+            out[j0] = vis.neuron(net.boff[l] + j0, last, fb_add(a0, b[j0]));
+        }
+        T *t = in; in = out; out = t;
+    }
+    return in[0];
+}
+
+template <typename T>
+struct FbGenReluVisit {
+    __device__ __forceinline__ T neuron(int, bool last, T pre) { return last ? pre : (fb_pos(pre) ? pre : (T)0); }
+};
+
+template <typename T>
+struct FbGenMaskedVisit {
+    const uint32_t *dead;     // [NW] or nullptr
+    __device__ __forceinline__ T neuron(int idx, bool last, T pre)
+    {
+        if (last) return pre;
+        bool keep = fb_pos(pre);
+        if (dead) keep = keep && !((dead[idx >> 5] >> (idx & 31)) & 1u);
+        return keep ? pre : (T)0;
+    }
+};
+
+// warp-cooperative counting: every lane of the warp reaches neuron() together (uniform control flow)
+struct FbGenCountVisit {
+    uint32_t *cnt;     // this warp's [N] counters in shared memory
+    bool active;
+    int lane;
+    __device__ __forceinline__ double neuron(int idx, bool last, double pre)
+    {
+        const bool nz = last ? fb_nonzero(pre) : fb_pos(pre);
+        const uint32_t bal = __ballot_sync(0xffffffffu, nz && active);
+        if (lane == (idx & 31)) cnt[idx] += __popc(bal);
+        return last ? pre : (fb_pos(pre) ? pre : 0.0);
+    }
+};
+
+// weights (float64) staged once per CTA into dynamic shared memory: [P] weights, [N] biases, then
+// per-warp uint32 counters [warps][N].
+template <bool PHILOX>
+__global__ void __launch_bounds__(FB_PROFILE_THREADS)
+fb_profile_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes,
+                      const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp, int chunks,
+                      int chunk_len, uint32_t *__restrict__ counts)
+{
+    extern __shared__ __align__(16) unsigned char fb_smem[];
+    double *sW = reinterpret_cast<double *>(fb_smem);
+    double *sB = sW + net.P;
+    uint32_t *sC = reinterpret_cast<uint32_t *>(sB + net.N);
+    for (int k = threadIdx.x; k < net.P; k += blockDim.x) sW[k] = net.W64[k];
+    for (int k = threadIdx.x; k < net.N; k += blockDim.x) sB[k] = net.B64[k];
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int D0 = net.dims[0], N = net.N;
+    uint32_t *cnt = sC + wib * N;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    const int64_t units = n * chunks;
+    double a[FB_MAXW], y[FB_MAXW];
+    for (int64_t u = gwarp; u < units; u += nwarps) {
+        const int64_t p = u / chunks;
+        const int c = (int)(u - p * chunks);
+        const int s0 = c * chunk_len;
+        const int s1 = min(nsamp, s0 + chunk_len);
+        for (int k = lane; k < N; k += 32) cnt[k] = 0;
+        __syncwarp();
+        const int32_t *box = boxes + p * (2 * D0);
+        const int64_t pidx = first_index + p;
+        FbGenCountVisit vis{cnt, false, lane};
+        for (int sb = s0; sb < s1; sb += 32) {
+            const int s = sb + lane;
+            vis.active = s < s1;
+            if (PHILOX) {
+                for (int blk = 0; blk * 4 < D0; ++blk) {
+                    uint32_t r[4];
+                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
+                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int i = blk * 4 + k;
+                        if (i < D0) {
+                            const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
+                            a[i] = (double)fb_map_range(r[k], lo, (uint32_t)(hi - lo + 1));
+                        }
+                    }
+                }
+            } else {
+                const int32_t *row = samples + ((int64_t)p * nsamp + (vis.active ? s : s0)) * D0;
+                for (int i = 0; i < D0; ++i) a[i] = (double)__ldg(row + i);
+            }
+            fb_gen_forward<double>(net, sW, sB, a, y, vis);
+        }
+        __syncwarp();
+        for (int k = lane; k < N; k += 32) {
+            if (chunks == 1) counts[p * N + k] = cnt[k];
+            else atomicAdd(&counts[p * N + k], cnt[k]);
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// interval recurrence, one warp per partition, one lane per neuron of the current layer; the layer's
+// input bounds sit in shared memory (broadcast reads), weights stream from global memory coalesced
+// across lanes (W[i][j], j = lane).
+// ---------------------------------------------------------------------------------------------------
+#define FB_IBP_GEN_WARPS 4
+
+__global__ void __launch_bounds__(FB_IBP_GEN_WARPS * 32)
+fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes, const uint32_t *__restrict__ counts,
+                  const double *__restrict__ tol, const FbPruneOut o)
+{
+    __shared__ double sb[FB_IBP_GEN_WARPS][8][FB_MAXW];      // lb, ub, lbd, ubd  x  {in, out}
+    __shared__ uint32_t sm[FB_IBP_GEN_WARPS][3][FB_MAX_NW];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int N = net.N, NW = (N + 31) / 32, D0 = net.dims[0];
+    const int64_t nwarps = (int64_t)gridDim.x * FB_IBP_GEN_WARPS;
+    for (int64_t p = (int64_t)blockIdx.x * FB_IBP_GEN_WARPS + wib; p < n; p += nwarps) {
+        double *lb = sb[wib][0], *ub = sb[wib][1], *lbd = sb[wib][2], *ubd = sb[wib][3];
+        double *nlb = sb[wib][4], *nub = sb[wib][5], *nlbd = sb[wib][6], *nubd = sb[wib][7];
+        uint32_t *cand_w = sm[wib][0], *bdead_w = sm[wib][1], *sliver_w = sm[wib][2];
+        for (int k = lane; k < NW; k += 32) { cand_w[k] = 0; bdead_w[k] = 0; sliver_w[k] = 0; }
+        for (int i = lane; i < D0; i += 32) {
+            const int lo = __ldg(boxes + p * (2 * D0) + 2 * i), hi = __ldg(boxes + p * (2 * D0) + 2 * i + 1);
+            lb[i] = lbd[i] = (double)lo; ub[i] = ubd[i] = (double)hi;
+        }
+        __syncwarp();
+        double out_lbd = 0.0, out_ubd = 0.0;
+        for (int l = 0; l < net.L; ++l) {
+            const int IN = net.dims[l], OUT = net.dims[l + 1], BO = net.boff[l];
+            const double *w = net.W64 + net.woff[l];
+            const bool last = (l == net.L - 1);
+            bool all1 = true;
+            for (int jb = 0; jb < OUT; jb += 32) {
+                const int j = jb + lane;
+                const bool live = j < OUT;
+                bool bd = true;
+                if (live) {
+                    double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
+                    for (int i = 0; i < IN; ++i) {
+                        const double wt = __ldg(w + (int64_t)i * OUT + j);
+                        const bool neg = fb_signbit(wt);
+                        const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+                        const double ad = neg ? ubd[i] : lbd[i], bdv = neg ? lbd[i] : ubd[i];
+                        mn = __dadd_rn(mn, __dmul_rn(wt, a));
+                        mx = __dadd_rn(mx, __dmul_rn(wt, b));
+                        mnd = __dadd_rd(mnd, __dmul_rd(wt, ad));
+                        mxd = __dadd_ru(mxd, __dmul_ru(wt, bdv));
+                    }
+                    const double bj = __ldg(net.B64 + BO + j);
+                    const double wl = __dadd_rn(mn, bj), wu = __dadd_rn(mx, bj);
+                    const double wld = __dadd_rd(mnd, bj), wud = __dadd_ru(mxd, bj);
+                    const int idx = BO + j;
+                    const uint32_t c32 = counts ? counts[p * N + idx] : 0u;
+                    const bool c = c32 == 0, le0 = wu <= 0.0;
+                    const uint32_t bit = 1u << (idx & 31);
+                    if (c) atomicOr(&cand_w[idx >> 5], bit);
+                    bd = last ? c : (c && le0);
+                    if (bd) atomicOr(&bdead_w[idx >> 5], bit);
+                    if (!last && tol != nullptr && c && !le0 && wu <= tol[idx]) atomicOr(&sliver_w[idx >> 5], bit);
+                    if (last) { out_lbd = wld; out_ubd = wud; }
+                    if (o.counts16) o.counts16[p * N + idx] = (uint16_t)c32;
+                    if (o.ws_lb) o.ws_lb[p * N + idx] = wl;
+                    if (o.ws_ub) o.ws_ub[p * N + idx] = wu;
+                    if (o.pl_lb) o.pl_lb[p * N + idx] = wl < 0.0 ? 0.0 : wl;
+                    if (o.pl_ub) o.pl_ub[p * N + idx] = wu < 0.0 ? 0.0 : wu;
+                    if (o.lb_rd) o.lb_rd[p * N + idx] = wld;
+                    if (o.ub_ru) o.ub_ru[p * N + idx] = wud;
+                    nlb[j] = wl < 0.0 ? 0.0 : wl; nub[j] = wu < 0.0 ? 0.0 : wu;
+                    nlbd[j] = wld < 0.0 ? 0.0 : wld; nubd[j] = wud < 0.0 ? 0.0 : wud;
+                }
+                all1 = __all_sync(0xffffffffu, !live || bd) && all1;
+            }
+            __syncwarp();
+            if (all1 && lane == 0) bdead_w[BO >> 5] &= ~(1u << (BO & 31));        // keep-one fix
+            double *t;
+            t = lb; lb = nlb; nlb = t; t = ub; ub = nub; nub = t;
+            t = lbd; lbd = nlbd; nlbd = t; t = ubd; ubd = nubd; nubd = t;
+            __syncwarp();
+        }
+        // the output neuron is lane 0 of the last layer
+        out_lbd = __shfl_sync(0xffffffffu, out_lbd, 0);
+        out_ubd = __shfl_sync(0xffffffffu, out_ubd, 0);
+        uint32_t anysl = 0;
+        for (int k = lane; k < NW; k += 32) {
+            if (o.cand) o.cand[p * NW + k] = cand_w[k];
+            if (o.b_dead) o.b_dead[p * NW + k] = bdead_w[k];
+            if (o.dead) o.dead[p * NW + k] = bdead_w[k];
+            if (o.sliver) o.sliver[p * NW + k] = sliver_w[k];
+            anysl |= sliver_w[k];
+        }
+        anysl = __reduce_or_sync(0xffffffffu, anysl);
+        if (lane == 0 && o.verdict) {
+            uint8_t v = 0;
+            if (out_lbd > 0.0 || out_ubd < 0.0) v |= FB_VERDICT_CERTIFIED;
+            if (anysl) v |= FB_VERDICT_SLIVER;
+            o.verdict[p] = v;
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// logits / pair screen / partition screen, generic shapes: weights read through L1 (__ldg).
+// ---------------------------------------------------------------------------------------------------
+template <typename T> struct FbNetPtr;
+template <> struct FbNetPtr<double> {
+    static __device__ __forceinline__ const double *W(const GenNet &n) { return n.W64; }
+    static __device__ __forceinline__ const double *B(const GenNet &n) { return n.B64; }
+};
+template <> struct FbNetPtr<float> {
+    static __device__ __forceinline__ const float *W(const GenNet &n) { return n.W32; }
+    static __device__ __forceinline__ const float *B(const GenNet &n) { return n.B32; }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(FB_FWD_THREADS)
+fb_forward_gen_kernel(const GenNet net, int64_t m, const T *__restrict__ X, const uint32_t *__restrict__ dead_bits,
+                      T *__restrict__ logits)
+{
+    const int D0 = net.dims[0];
+    T a[FB_MAXW], y[FB_MAXW];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+        for (int i = 0; i < D0; ++i) a[i] = X[r * D0 + i];
+        FbGenMaskedVisit<T> vis{dead_bits};
+        logits[r] = fb_gen_forward<T>(net, FbNetPtr<T>::W(net), FbNetPtr<T>::B(net), a, y, vis);
+    }
+}
+
+__global__ void __launch_bounds__(FB_FWD_THREADS)
+fb_pair_screen_gen_kernel(const GenNet net, int64_t m, const float *__restrict__ X, const FbPaCols pa, int k_alts,
+                          const float *__restrict__ alts, uint8_t *__restrict__ orig_pred, int32_t *__restrict__ first_flip)
+{
+    const int D0 = net.dims[0];
+    float a[FB_MAXW], y[FB_MAXW];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+        const float *x0 = X + r * D0;
+        for (int i = 0; i < D0; ++i) a[i] = x0[i];
+        FbGenReluVisit<float> vis;
+        const bool p0 = fb_pos(fb_gen_forward<float>(net, net.W32, net.B32, a, y, vis));
+        int flip = -1;
+        for (int al = 0; al < k_alts && flip < 0; ++al) {
+            for (int i = 0; i < D0; ++i) a[i] = x0[i];
+            bool same = true;
+            for (int q = 0; q < pa.n; ++q) {
+                const float v = __ldg(alts + al * pa.n + q);
+                same = same && (v == x0[pa.col[q]]);
+                a[pa.col[q]] = v;
+            }
+            if (same) continue;
+            const bool p1 = fb_pos(fb_gen_forward<float>(net, net.W32, net.B32, a, y, vis));
+            if (p1 != p0) flip = al;
+        }
+        orig_pred[r] = p0 ? 1 : 0;
+        first_flip[r] = flip;
+    }
+}
+
+template <bool PHILOX>
+__global__ void __launch_bounds__(FB_PROFILE_THREADS)
+fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes,
+                               const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp,
+                               int chunks, int chunk_len, int pa_col, unsigned long long *__restrict__ ce_key)
+{
+    const int D0 = net.dims[0];
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t units = n * chunks;
+    float x0[FB_MAXW], a[FB_MAXW], y[FB_MAXW];
+    for (int64_t u = gwarp; u < units; u += nwarps) {
+        const int64_t p = u / chunks;
+        const int c = (int)(u - p * chunks);
+        const int s0 = c * chunk_len;
+        const int s1 = min(nsamp, s0 + chunk_len);
+        const int32_t *box = boxes + p * (2 * D0);
+        const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
+        const int64_t pidx = first_index + p;
+        unsigned long long best = ~0ull;
+        for (int sb = s0; sb < s1; sb += 32) {
+            const int s = sb + lane;
+            const bool active = s < s1;
+            if (PHILOX) {
+                for (int blk = 0; blk * 4 < D0; ++blk) {
+                    uint32_t r[4];
+                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
+                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int i = blk * 4 + k;
+                        if (i < D0) {
+                            const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
+                            x0[i] = (float)fb_map_range(r[k], lo, (uint32_t)(hi - lo + 1));
+                        }
+                    }
+                }
+            } else {
+                const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
+                for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);
+            }
+            bool havep = false, haven = false;
+            int vp = 0, vn = 0;
+            FbGenReluVisit<float> vis;
+            for (int v = pa_lo; v <= pa_hi; ++v) {
+                for (int i = 0; i < D0; ++i) a[i] = x0[i];
+                a[pa_col] = (float)v;
+                const float yv = fb_gen_forward<float>(net, net.W32, net.B32, a, y, vis);
+                if (yv > 0.0f && !havep) { havep = true; vp = v; }
+                if (yv < 0.0f && !haven) { haven = true; vn = v; }
+            }
+            const bool ce = active && havep && haven;
+            if (ce && best == ~0ull)
+                best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)(vp - pa_lo) << 16) |
+                       (unsigned long long)(uint32_t)(vn - pa_lo);
+            if (__any_sync(0xffffffffu, ce)) break;
+        }
+        const uint32_t hi = (uint32_t)(best >> 32);
+        const uint32_t hmin = __reduce_min_sync(0xffffffffu, hi);
+        if (hmin != 0xffffffffu && hi == hmin) atomicMin(&ce_key[p], best);
+    }
+}

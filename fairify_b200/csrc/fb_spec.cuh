@@ -1,0 +1,433 @@
+// fb_spec.cuh -- compile-time-specialised kernels (see fb_common.cuh).
+//
+// Every loop over neurons / inputs is fully unrolled; weights are immediate constant-bank operands
+// (the parameter struct is __grid_constant__), activations and interval bounds are registers.  The FP64
+// pipe is the only unit these kernels lean on: per sample P DFMA + N DADD (profile), per box
+// 8P + 4N directed/nearest DMUL/DADD (interval recurrence).
+#pragma once
+#include "fb_common.cuh"
+
+// ---------------------------------------------------------------------------------------------------
+// forward pass, one sample per thread.  reference: layer_net / net, utils/AC-1-Model-Functions.py:16-32
+// Visit::neuron(idx, last, pre) returns the activation fed to the next layer; idx and last fold to
+// constants because every call site is inside fully unrolled loops.
+// ---------------------------------------------------------------------------------------------------
+template <class S, int l, typename T, class Visit>
+__device__ __forceinline__ T fb_spec_forward(const SpecParams<S, T> &prm, const T (&x)[S::dim(l)], Visit &v)
+{
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
+    constexpr bool last = (l == S::NL - 1);
+    T y[OUT];
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) {
+        T acc = (T)0;
+#pragma unroll
+        for (int i = 0; i < IN; ++i) acc = fb_fma(prm.w[WO + i * OUT + j], x[i], acc);
+        const T pre = fb_add(acc, prm.b[BO + j]);
+        y[j] = v.neuron(BO + j, last, pre);
+    }
+    if constexpr (last) return y[0];
+    else return fb_spec_forward<S, l + 1, T, Visit>(prm, y, v);
+}
+
+// plain ReLU visitor (logit only)
+template <typename T>
+struct FbReluVisit {
+    __device__ __forceinline__ T neuron(int, bool last, T pre) { return last ? pre : (fb_pos(pre) ? pre : (T)0); }
+};
+
+// ReLU + "these neurons are pruned" visitor (dead activations forced to 0 == reference prune_neurons,
+// utils/prune.py:950-977, which deletes the column and the next layer's row)
+template <typename T, int NW>
+struct FbMaskedVisit {
+    uint32_t dead[NW];
+    __device__ __forceinline__ T neuron(int idx, bool last, T pre)
+    {
+        if (last) return pre;
+        const bool keep = fb_pos(pre) && !((dead[idx >> 5] >> (idx & 31)) & 1u);
+        return keep ? pre : (T)0;
+    }
+};
+
+// activation-profile visitor: per-lane packed 8-bit counters, one field per neuron.
+// reference: candidate_dead_nodes, utils/prune.py:175-180 (activation != 0, output layer included)
+template <int N>
+struct FbCountVisit {
+    uint32_t cnt[(N + 3) / 4];
+    bool active;
+    __device__ __forceinline__ double neuron(int idx, bool last, double pre)
+    {
+        const bool nz = last ? fb_nonzero(pre) : fb_pos(pre);
+        if (nz && active) cnt[idx >> 2] += 1u << (8 * (idx & 3));
+        return last ? pre : (fb_pos(pre) ? pre : 0.0);
+    }
+};
+
+#define FB_PROFILE_THREADS 128
+#define FB_PROFILE_MAX_STEPS 255     // 8-bit per-lane counters
+
+// One warp per (partition, sample chunk); lanes are samples.
+// counts[p][N] (uint32): stored when chunks == 1, atomically added otherwise (caller zeroes first).
+template <class S, bool PHILOX>
+__global__ void __launch_bounds__(FB_PROFILE_THREADS)
+fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
+                       const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
+                       int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *__restrict__ counts)
+{
+    constexpr int D0 = S::D0, N = S::N;
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t units = n * chunks;
+    for (int64_t u = gwarp; u < units; u += nwarps) {
+        const int64_t p = u / chunks;
+        const int c = (int)(u - p * chunks);
+        const int s0 = c * chunk_len;
+        const int s1 = min(nsamp, s0 + chunk_len);
+        int32_t lo[D0];
+        uint32_t range[D0];
+        if (PHILOX) {
+            const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+#pragma unroll
+            for (int i = 0; i < D0; ++i) {
+                const int2 b = __ldg(bx + i);
+                lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
+            }
+        }
+        FbCountVisit<N> vis;
+#pragma unroll
+        for (int k = 0; k < (N + 3) / 4; ++k) vis.cnt[k] = 0;
+        const int64_t pidx = first_index + p;
+        for (int sb = s0; sb < s1; sb += 32) {
+            const int s = sb + lane;
+            vis.active = s < s1;
+            double x[D0];
+            if (PHILOX) {
+#pragma unroll
+                for (int blk = 0; blk * 4 < D0; ++blk) {
+                    uint32_t r[4];
+                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
+                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (blk * 4 + k < D0) x[blk * 4 + k] = (double)fb_map_range(r[k], lo[blk * 4 + k], range[blk * 4 + k]);
+                }
+            } else {
+                const int32_t *row = samples + ((int64_t)p * nsamp + (vis.active ? s : s0)) * D0;
+#pragma unroll
+                for (int i = 0; i < D0; ++i) x[i] = (double)__ldg(row + i);
+            }
+            fb_spec_forward<S, 0, double>(prm, x, vis);
+        }
+        uint32_t mine = 0;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            const uint32_t tot = __reduce_add_sync(0xffffffffu, (vis.cnt[j >> 2] >> (8 * (j & 3))) & 0xffu);
+            if ((j & 31) == lane) mine = tot;
+            if ((j & 31) == 31 || j == N - 1) {
+                const int jj = (j & ~31) + lane;
+                if (jj <= j) {
+                    if (chunks == 1) counts[p * N + jj] = mine;
+                    else atomicAdd(&counts[p * N + jj], mine);
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// interval recurrence + mask algebra, one partition per thread.
+// reference: neuron_bounds utils/prune.py:105-164 (round-to-nearest chain, separately rounded product
+// and sum), dead_node_from_bound :226-251, keep-one fix :689-691, merge :941-948.  The second chain
+// rounds outward (lower bound toward -inf, upper toward +inf) and is what the verdict and the reported
+// enclosure use.
+// ---------------------------------------------------------------------------------------------------
+struct FbPruneOut {
+    uint32_t *cand;       // [n][NW]  count == 0
+    uint32_t *b_dead;     // [n][NW]  cand & (ws_ub <= 0), keep-one applied
+    uint32_t *dead;       // [n][NW]  b_dead | s_dead (s_dead == 0 on device), keep-one applied
+    uint32_t *sliver;     // [n][NW]  neurons whose s_dead needs the host Z3 query
+    uint8_t *verdict;     // [n]
+    uint16_t *counts16;   // [n][N]   non-zero activation counts (pos_prob * S)
+    double *ws_lb, *ws_ub, *pl_lb, *pl_ub;   // [n][N]  round-to-nearest, reference-exact
+    double *lb_rd, *ub_ru;                   // [n][N]  outward rounded
+};
+
+template <class S>
+struct FbIbpSink {
+    static constexpr int N = S::N, NW = S::NW;
+    const uint32_t *cnt;      // this partition's counts or nullptr (then every neuron is a candidate)
+    const double *tol;        // [N] or nullptr
+    const FbPruneOut &o;
+    int64_t p;
+    uint32_t cand_w[NW], bdead_w[NW], sliver_w[NW];
+    double out_lb_rd, out_ub_ru;
+
+    __device__ __forceinline__ FbIbpSink(const FbPruneOut &o_, int64_t p_, const uint32_t *cnt_, const double *tol_)
+        : cnt(cnt_), tol(tol_), o(o_), p(p_)
+    {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) { cand_w[k] = 0; bdead_w[k] = 0; sliver_w[k] = 0; }
+    }
+
+    // idx / last are compile-time constants after unrolling (the call sits in fully unrolled loops)
+    __device__ __forceinline__ void neuron(int idx, bool last, double lb, double ub, double lbd, double ubd)
+    {
+        uint32_t c32 = 0;
+        if (cnt) c32 = cnt[idx];
+        const bool c = c32 == 0;
+        const bool le0 = ub <= 0.0;
+        const uint32_t bit = 1u << (idx & 31);
+        if (c) cand_w[idx >> 5] |= bit;
+        if (last) { if (c) bdead_w[idx >> 5] |= bit; out_lb_rd = lbd; out_ub_ru = ubd; }
+        else {
+            if (c && le0) bdead_w[idx >> 5] |= bit;
+            if (tol != nullptr && c && !le0 && ub <= tol[idx]) sliver_w[idx >> 5] |= bit;
+        }
+        if (o.counts16) o.counts16[p * N + idx] = (uint16_t)c32;
+        if (o.ws_lb) o.ws_lb[p * N + idx] = lb;
+        if (o.ws_ub) o.ws_ub[p * N + idx] = ub;
+        if (o.pl_lb) o.pl_lb[p * N + idx] = lb < 0.0 ? 0.0 : lb;
+        if (o.pl_ub) o.pl_ub[p * N + idx] = ub < 0.0 ? 0.0 : ub;
+        if (o.lb_rd) o.lb_rd[p * N + idx] = lbd;
+        if (o.ub_ru) o.ub_ru[p * N + idx] = ubd;
+    }
+
+    // keep-one fix for the layer occupying bits [BO, BO+OUT)
+    template <int BO, int OUT>
+    __device__ __forceinline__ void keep_one()
+    {
+        bool all1 = true;
+#pragma unroll
+        for (int k = BO >> 5; k <= (BO + OUT - 1) >> 5; ++k) {
+            const int b0 = (k * 32 > BO) ? k * 32 : BO;
+            const int b1 = ((k + 1) * 32 < BO + OUT) ? (k + 1) * 32 : BO + OUT;
+            const uint32_t m = (b1 - b0 == 32) ? 0xffffffffu : (((1u << (b1 - b0)) - 1u) << (b0 & 31));
+            all1 = all1 && ((bdead_w[k] & m) == m);
+        }
+        if (all1) bdead_w[BO >> 5] &= ~(1u << (BO & 31));
+    }
+
+    __device__ __forceinline__ void finish()
+    {
+        uint32_t anysl = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (o.cand) o.cand[p * NW + k] = cand_w[k];
+            if (o.b_dead) o.b_dead[p * NW + k] = bdead_w[k];
+            if (o.dead) o.dead[p * NW + k] = bdead_w[k];
+            if (o.sliver) o.sliver[p * NW + k] = sliver_w[k];
+            anysl |= sliver_w[k];
+        }
+        if (o.verdict) {
+            uint8_t v = 0;
+            if (out_lb_rd > 0.0 || out_ub_ru < 0.0) v |= FB_VERDICT_CERTIFIED;
+            if (anysl) v |= FB_VERDICT_SLIVER;
+            o.verdict[p] = v;
+        }
+    }
+};
+
+template <class S, int l>
+__device__ __forceinline__ void fb_spec_ibp(const SpecParams<S, double> &prm, const double (&lb)[S::dim(l)],
+                                            const double (&ub)[S::dim(l)], const double (&lbd)[S::dim(l)],
+                                            const double (&ubd)[S::dim(l)], FbIbpSink<S> &sink)
+{
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
+    constexpr bool last = (l == S::NL - 1);
+    double nlb[OUT], nub[OUT], nlbd[OUT], nubd[OUT];
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) {
+        double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+            const double w = prm.w[WO + i * OUT + j];
+            const bool neg = fb_signbit(w);            // host canonicalises -0.0 to +0.0
+            const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+            const double ad = neg ? ubd[i] : lbd[i], bd = neg ? lbd[i] : ubd[i];
+            mn = __dadd_rn(mn, __dmul_rn(w, a));
+            mx = __dadd_rn(mx, __dmul_rn(w, b));
+            mnd = __dadd_rd(mnd, __dmul_rd(w, ad));
+            mxd = __dadd_ru(mxd, __dmul_ru(w, bd));
+        }
+        const double bj = prm.b[BO + j];
+        const double wl = __dadd_rn(mn, bj), wu = __dadd_rn(mx, bj);
+        const double wld = __dadd_rd(mnd, bj), wud = __dadd_ru(mxd, bj);
+        sink.neuron(BO + j, last, wl, wu, wld, wud);
+        nlb[j] = wl < 0.0 ? 0.0 : wl; nub[j] = wu < 0.0 ? 0.0 : wu;
+        nlbd[j] = wld < 0.0 ? 0.0 : wld; nubd[j] = wud < 0.0 ? 0.0 : wud;
+    }
+    sink.template keep_one<BO, OUT>();
+    if constexpr (!last) fb_spec_ibp<S, l + 1>(prm, nlb, nub, nlbd, nubd, sink);
+}
+
+#define FB_IBP_THREADS 128
+
+template <class S>
+__global__ void __launch_bounds__(FB_IBP_THREADS)
+fb_ibp_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n, const int32_t *__restrict__ boxes,
+                   const uint32_t *__restrict__ counts, const double *__restrict__ tol,
+                   const __grid_constant__ FbPruneOut out)
+{
+    constexpr int D0 = S::D0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        double lb[D0], ub[D0];
+        const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+#pragma unroll
+        for (int i = 0; i < D0; ++i) {
+            const int2 b = __ldg(bx + i);
+            lb[i] = (double)b.x; ub[i] = (double)b.y;
+        }
+        FbIbpSink<S> sink(out, p, counts ? counts + p * S::N : nullptr, tol);
+        fb_spec_ibp<S, 0>(prm, lb, ub, lb, ub, sink);
+        sink.finish();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// logits for a batch of rows, one row per thread (get_y_pred / C-check, utils/verif_utils.py:1040-1047,
+// src/AC/Verify-AC.py:229-249).  T = double for integer / float64 rows, float for float32 rows.
+// ---------------------------------------------------------------------------------------------------
+#define FB_FWD_THREADS 128
+
+template <class S, typename T>
+__global__ void __launch_bounds__(FB_FWD_THREADS)
+fb_forward_spec_kernel(const __grid_constant__ SpecParams<S, T> prm, int64_t m, const T *__restrict__ X,
+                       const uint32_t *__restrict__ dead_bits, T *__restrict__ logits)
+{
+    constexpr int D0 = S::D0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+        T x[D0];
+#pragma unroll
+        for (int i = 0; i < D0; ++i) x[i] = X[r * D0 + i];
+        FbMaskedVisit<T, S::NW> vis;
+#pragma unroll
+        for (int k = 0; k < S::NW; ++k) vis.dead[k] = dead_bits ? dead_bits[k] : 0u;
+        logits[r] = fb_spec_forward<S, 0, T>(prm, x, vis);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// prediction side of CausalDiscriminationDetector.causal_discrimination, src/AC/metrics.py:130-159:
+// per base row the original class and the first alternative protected assignment whose class differs.
+// ---------------------------------------------------------------------------------------------------
+#define FB_MAX_PA 4
+
+struct FbPaCols { int n; int col[FB_MAX_PA]; };
+
+template <class S>
+__global__ void __launch_bounds__(FB_FWD_THREADS)
+fb_pair_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int64_t m, const float *__restrict__ X,
+                           const FbPaCols pa, int k_alts, const float *__restrict__ alts,
+                           uint8_t *__restrict__ orig_pred, int32_t *__restrict__ first_flip)
+{
+    constexpr int D0 = S::D0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+        float x0[D0];
+#pragma unroll
+        for (int i = 0; i < D0; ++i) x0[i] = X[r * D0 + i];
+        FbReluVisit<float> vis;
+        const bool p0 = fb_pos(fb_spec_forward<S, 0, float>(prm, x0, vis));
+        int flip = -1;
+        for (int a = 0; a < k_alts && flip < 0; ++a) {
+            float x[D0];
+#pragma unroll
+            for (int i = 0; i < D0; ++i) x[i] = x0[i];
+            bool same = true;
+            for (int q = 0; q < pa.n; ++q) {
+                const float v = __ldg(alts + a * pa.n + q);
+#pragma unroll
+                for (int i = 0; i < D0; ++i)
+                    if (i == pa.col[q]) { same = same && (v == x0[i]); x[i] = v; }
+            }
+            if (same) continue;
+            const bool p1 = fb_pos(fb_spec_forward<S, 0, float>(prm, x, vis));
+            if (p1 != p0) flip = a;
+        }
+        orig_pred[r] = p0 ? 1 : 0;
+        first_flip[r] = flip;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// per-partition sampled counterexample screen (the property the drivers hand to Z3,
+// src/AC/Verify-AC.py:137-156): one warp per (partition, chunk), lanes are samples; the protected
+// column is swept over the partition's own range.  Result: packed 64-bit key
+// (sample << 32 | (v_pos - lo) << 16 | (v_neg - lo)), atomicMin'ed into ce_key[p] (pre-set to ~0).
+// ---------------------------------------------------------------------------------------------------
+template <class S, bool PHILOX>
+__global__ void __launch_bounds__(FB_PROFILE_THREADS)
+fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int64_t n,
+                                const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
+                                int64_t first_index, int nsamp, int chunks, int chunk_len, int pa_col,
+                                unsigned long long *__restrict__ ce_key)
+{
+    constexpr int D0 = S::D0;
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t units = n * chunks;
+    for (int64_t u = gwarp; u < units; u += nwarps) {
+        const int64_t p = u / chunks;
+        const int c = (int)(u - p * chunks);
+        const int s0 = c * chunk_len;
+        const int s1 = min(nsamp, s0 + chunk_len);
+        int32_t lo[D0];
+        uint32_t range[D0];
+        int pa_lo = 0, pa_hi = 0;
+        {
+            const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+#pragma unroll
+            for (int i = 0; i < D0; ++i) {
+                const int2 b = __ldg(bx + i);
+                lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
+                if (i == pa_col) { pa_lo = b.x; pa_hi = b.y; }
+            }
+        }
+        const int64_t pidx = first_index + p;
+        unsigned long long best = ~0ull;
+        for (int sb = s0; sb < s1; sb += 32) {
+            const int s = sb + lane;
+            const bool active = s < s1;
+            float x0[D0];
+            if (PHILOX) {
+#pragma unroll
+                for (int blk = 0; blk * 4 < D0; ++blk) {
+                    uint32_t r[4];
+                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
+                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (blk * 4 + k < D0) x0[blk * 4 + k] = (float)fb_map_range(r[k], lo[blk * 4 + k], range[blk * 4 + k]);
+                }
+            } else {
+                const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
+#pragma unroll
+                for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);
+            }
+            bool havep = false, haven = false;
+            int vp = 0, vn = 0;
+            FbReluVisit<float> vis;
+            for (int v = pa_lo; v <= pa_hi; ++v) {
+                float x[D0];
+#pragma unroll
+                for (int i = 0; i < D0; ++i) x[i] = (i == pa_col) ? (float)v : x0[i];
+                const float y = fb_spec_forward<S, 0, float>(prm, x, vis);
+                if (y > 0.0f && !havep) { havep = true; vp = v; }
+                if (y < 0.0f && !haven) { haven = true; vn = v; }
+            }
+            const bool ce = active && havep && haven;
+            if (ce && best == ~0ull)
+                best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)(vp - pa_lo) << 16) |
+                       (unsigned long long)(uint32_t)(vn - pa_lo);
+            if (__any_sync(0xffffffffu, ce)) break;          // later samples cannot beat this step's
+        }
+        // lowest sample index wins; keys are unique per sample so min over the packed key is enough
+        const uint32_t hi = (uint32_t)(best >> 32);
+        const uint32_t hmin = __reduce_min_sync(0xffffffffu, hi);
+        if (hmin != 0xffffffffu && hi == hmin) atomicMin(&ce_key[p], best);
+    }
+}

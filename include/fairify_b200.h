@@ -1,0 +1,125 @@
+/*
+ * fairify_b200.h -- C ABI of libfairify_b200.so: Fairify's data-parallel pre-solver stage on B200 (sm_100a).
+ *
+ * Plain pointers and sizes only.  Unless a function name ends in _host, every data pointer is a DEVICE
+ * pointer on the device that was current when the model was created, and `stream` is a cudaStream_t
+ * passed as void* (NULL = the legacy default stream).  Functions return 0 on success, a non-zero code on
+ * failure; fb_last_error() then returns a thread-local description.  There is no CPU fallback: without
+ * a usable CUDA device every compute entry point fails.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the Fairify checkout).
+ *
+ * Layouts
+ *   weights   float32, layer-major, each layer [in][out] row-major -- exactly what
+ *             `model.layers[i].get_weights()` returns in the drivers (src/AC/Verify-AC.py:97-99)
+ *   boxes     int32 [n][d][2] = (lo, hi) per feature in DataFrame COLUMN order
+ *             (the order utils/prune.py:108-114 looks the range_dict up in)
+ *   samples   int32 [n][S][d], or NULL to draw them on the device (Philox4x32-10, counter =
+ *             (sample, partition index, feature/4), key = seed)
+ *   masks     uint32 [n][NW], NW = ceil(N/32); bit k = neuron k, neurons numbered layer by layer,
+ *             output neuron included (N = sum of layer widths)
+ *   per-neuron arrays  [n][N] in the same numbering
+ */
+#ifndef FAIRIFY_B200_H
+#define FAIRIFY_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FB_OK 0
+#define FB_ERR_INVALID 1      /* bad argument */
+#define FB_ERR_CUDA 2         /* CUDA runtime error (message has the cudaError string) */
+#define FB_ERR_UNSUPPORTED 3  /* shape outside the supported envelope */
+#define FB_ERR_NOMEM 4
+
+#define FB_VERDICT_CERTIFIED 1u /* logit provably > 0 or < 0 on the whole box: no counterexample exists */
+#define FB_VERDICT_CE 2u        /* the sampled screen found a counterexample pair */
+#define FB_VERDICT_SLIVER 4u    /* a bound is within rounding error of 0: host must run the Z3 neuron check */
+
+typedef struct fb_model fb_model;
+typedef struct fb_grid fb_grid;
+
+/* Outputs of the prune stage; any pointer may be NULL (that output is skipped). */
+typedef struct fb_prune_out {
+    uint32_t *cand;     /* candidates: never active on the samples      (candidate_dead_nodes, utils/prune.py:183-187) */
+    uint32_t *b_dead;   /* b_dead_node_mask after the keep-one fix       (dead_node_from_bound :226-251, :689-691)     */
+    uint32_t *dead;     /* dead_nodes = merge(b_dead, s_dead) + keep-one (:702-705); s_dead is 0 unless `sliver`       */
+    uint32_t *sliver;   /* neurons the host must hand to singular_verification (:276-356)                              */
+    uint8_t *verdict;   /* [n] FB_VERDICT_* bits                                                                       */
+    uint16_t *counts;   /* [n][N] non-zero activation counts; pos_prob = counts / S (:188-191)                         */
+    double *ws_lb, *ws_ub, *pl_lb, *pl_ub; /* [n][N] neuron_bounds, round-to-nearest, reference-exact (:105-164)      */
+    double *lb_rd, *ub_ru;                 /* [n][N] outward-rounded enclosure of the same recurrence                  */
+} fb_prune_out;
+
+/* -- library ---------------------------------------------------------------------------------- */
+int fb_version(void);
+const char *fb_last_error(void);
+/* number of SMs of the current device (grid sizing; 148 on B200) */
+int fb_num_sms(int *out);
+
+/* -- model: replaces the (w, b) lists every hot-path function receives -------------------------- */
+/* L weight layers, dims[L+1] = {d, h1, ..., 1}.  Weights are converted to float64 once (exact). */
+int fb_model_create(int L, const int32_t *dims, const float *w_host, const float *b_host, fb_model **out);
+void fb_model_destroy(fb_model *m);
+/* N = neurons, P = weights, specialised = 1 when a compile-time-unrolled kernel set serves this shape */
+int fb_model_info(const fb_model *m, int *L, int *N, int *P, int *specialised);
+
+/* -- partition grid: utils/input_partition.py:17-46 `partition`, :48-76 `partitioned_ranges` ---- */
+/* lo/hi in column order, T = PARTITION_THRESHOLD, key_order[k] = column index of the k-th range_dict key */
+int fb_grid_create(int d, const int64_t *lo, const int64_t *hi, int64_t T, const int32_t *key_order, fb_grid **out);
+void fb_grid_destroy(fb_grid *g);
+int64_t fb_grid_size(const fb_grid *g);
+/* boxes [count][d][2] for canonical (itertools.product) indices first .. first+count-1 */
+int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int32_t *boxes, void *stream);
+
+/* -- activation profile: candidate_dead_nodes, utils/prune.py:168-192 (+ simluate_data :205-222) -- */
+/* counts uint32 [n][N].  first_index = global index of boxes[0] (Philox counter; keeps shards identical) */
+int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+               int64_t first_index, uint32_t *counts, void *stream);
+
+/* -- interval bounds + masks: neuron_bounds :105-164, dead_node_from_bound :226-251, keep-one fix,
+ *    merge_dead_nodes :941-948.  counts may be NULL (bounds-only run: every neuron is a candidate);
+ *    tol [N] may be NULL (no sliver detection). */
+int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const uint32_t *counts, const double *tol,
+           const fb_prune_out *out, void *stream);
+
+/* -- the whole pre-solver stage for a batch of boxes: sound_prune*, utils/prune.py:671-859, minus the
+ *    Z3 neuron queries (reported through `sliver`).  Allocates [n][N] uint32 of scratch per call. */
+int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+             int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
+
+/* Same with HOST buffers in and out (boxes, samples, tol and every non-NULL output are host pointers;
+ * pinned memory makes the copies asynchronous).  Copies in, runs, copies out, synchronises the stream. */
+int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                  int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
+
+/* -- logits: `net`, utils/<MODEL>-Model-Functions.py (e.g. AC-1 :25-32); get_y_pred utils/verif_utils.py:1040-1047.
+ *    dead_bits [NW] or NULL: neurons forced to 0 (== the pruned network of prune_neurons, utils/prune.py:950-977). */
+int fb_forward_f64(const fb_model *m, int64_t rows, const double *X, const uint32_t *dead_bits, double *logits, void *stream);
+int fb_forward_f32(const fb_model *m, int64_t rows, const float *X, const uint32_t *dead_bits, float *logits, void *stream);
+
+/* -- pair screen: the predictions of CausalDiscriminationDetector.causal_discrimination, src/AC/metrics.py:130-159.
+ *    X float32 [rows][d]; pa_cols (host) = protected columns; alts float32 [k][n_pa] (device) = every protected
+ *    assignment in itertools.product order.  orig_pred[r] = class of row r; first_flip[r] = index of the first
+ *    alternative (different from the row's own assignment) whose class differs, or -1. */
+int fb_pair_screen(const fb_model *m, int64_t rows, const float *X, int n_pa, const int32_t *pa_cols_host, int k_alts,
+                   const float *alts, uint8_t *orig_pred, int32_t *first_flip, void *stream);
+
+/* -- per-partition sampled counterexample screen (the property src/AC/Verify-AC.py:137-156 gives Z3).
+ *    ce_sample/pa_pos/pa_neg int32 [n]: lowest sample index that is a counterexample and the protected
+ *    values with logit > 0 / < 0, or -1.  verdict (may be NULL) gets FB_VERDICT_CE OR-ed in. */
+int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                        uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
+                        int32_t *pa_neg, uint8_t *verdict, void *stream);
+
+/* -- measurement aid: sustained DFMA issue rate of the current device, in TFLOP/s (FMA = 2 flops).
+ *    This is the roofline denominator of the profile / interval kernels. */
+int fb_fp64_peak(int iters, double *tflops, double *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FAIRIFY_B200_H */

@@ -1,0 +1,197 @@
+"""ctypes front end of the CPU oracle (oracle/fairify_oracle.c).
+
+TEST INFRASTRUCTURE ONLY -- see the header of fairify_oracle.c.  Nothing under fairify_b200/ or utils/
+imports this module; only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs do.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libfairify_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "fairify_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        _lib = C.CDLL(_SO)
+        _lib.fo_grid_count.restype = C.c_int64
+        _lib.fo_compression_ratio.restype = C.c_double
+        for f in ("fo_np_sum", "fo_np_mean", "fo_np_median_sorted", "fo_np_percentile_sorted"):
+            getattr(_lib, f).restype = C.c_double
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Net:
+    """Weights packed the way the oracle (and the device library) take them."""
+
+    def __init__(self, w, b):
+        self.L = len(w)
+        self.dims = np.array([w[0].shape[0]] + [x.shape[1] for x in w], dtype=np.int32)
+        self.W32 = np.concatenate([np.ascontiguousarray(x, dtype=np.float32).ravel() for x in w])
+        self.B32 = np.concatenate([np.ascontiguousarray(x, dtype=np.float32).ravel() for x in b])
+        self.W = self.W32.astype(np.float64)
+        self.B = self.B32.astype(np.float64)
+        self.N = int(self.dims[1:].sum())
+        self.P = int(self.W.size)
+        self.d = int(self.dims[0])
+        self.boff = np.concatenate([[0], np.cumsum(self.dims[1:])]).astype(np.int64)
+
+    def split(self, flat):
+        """[N] (or [n, N]) flat per-neuron array -> list of per-layer arrays."""
+        return [flat[..., self.boff[l]:self.boff[l + 1]] for l in range(self.L)]
+
+
+def grid_count(lo, hi, T):
+    lo = np.ascontiguousarray(lo, dtype=np.int64); hi = np.ascontiguousarray(hi, dtype=np.int64)
+    nch = np.zeros(len(lo), dtype=np.int64)
+    n = lib().fo_grid_count(len(lo), _p(lo), _p(hi), C.c_int64(T), _p(nch))
+    return int(n), nch
+
+
+def grid_boxes(lo, hi, T, key_order, first, count):
+    lo = np.ascontiguousarray(lo, dtype=np.int64); hi = np.ascontiguousarray(hi, dtype=np.int64)
+    ko = np.ascontiguousarray(key_order, dtype=np.int32)
+    out = np.zeros((count, len(lo), 2), dtype=np.int32)
+    lib().fo_grid_boxes(len(lo), _p(lo), _p(hi), C.c_int64(T), _p(ko), C.c_int64(first), C.c_int64(count), _p(out))
+    return out
+
+
+def ibp(net, boxes):
+    boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
+    outs = [np.zeros((n, net.N)) for _ in range(4)]
+    lib().fo_ibp(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), _p(boxes), *[_p(o) for o in outs])
+    return outs
+
+
+def ibp_directed(net, boxes):
+    boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
+    outs = [np.zeros((n, net.N)) for _ in range(2)]
+    lib().fo_ibp_directed(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), _p(boxes), *[_p(o) for o in outs])
+    return outs
+
+
+def philox_samples(seed, first_index, boxes, S):
+    boxes = np.ascontiguousarray(boxes, dtype=np.int32); n, d = boxes.shape[0], boxes.shape[1]
+    out = np.zeros((n, S, d), dtype=np.int32)
+    lib().fo_philox_samples(C.c_uint64(seed), C.c_int64(first_index), C.c_int64(n), S, d, _p(boxes), _p(out))
+    return out
+
+
+def profile(net, samples):
+    samples = np.ascontiguousarray(samples, dtype=np.int32); n, S = samples.shape[0], samples.shape[1]
+    counts = np.zeros((n, net.N), dtype=np.uint32)
+    lib().fo_profile(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), S, _p(samples), _p(counts))
+    return counts
+
+
+def forward_f64(net, X):
+    X = np.ascontiguousarray(X, dtype=np.float64); m = X.shape[0]
+    out = np.zeros(m)
+    lib().fo_forward_f64(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(m), _p(X), _p(out))
+    return out
+
+
+def forward_f32(net, X):
+    X = np.ascontiguousarray(X, dtype=np.float32); m = X.shape[0]
+    out = np.zeros(m, dtype=np.float32)
+    lib().fo_forward_f32(net.L, _p(net.dims), _p(net.W32), _p(net.B32), C.c_int64(m), _p(X), _p(out))
+    return out
+
+
+def masks(net, counts, ws_ub, tol):
+    counts = np.ascontiguousarray(counts, dtype=np.uint32); n = counts.shape[0]
+    ws_ub = np.ascontiguousarray(ws_ub, dtype=np.float64); tol = np.ascontiguousarray(tol, dtype=np.float64)
+    names = ("cand", "b_dead", "b_cand", "s_dead", "dead", "sliver")
+    outs = {k: np.zeros((n, net.N), dtype=np.uint8) for k in names}
+    lib().fo_masks(net.L, _p(net.dims), C.c_int64(n), _p(counts), _p(ws_ub), _p(tol), *[_p(outs[k]) for k in names])
+    return outs
+
+
+def compression_ratio(mask):
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    return lib().fo_compression_ratio(int(mask.size), _p(mask))
+
+
+def heuristic_prune(net, ws_lb, ws_ub, cand, s_cand, deads, pct):
+    a = [np.ascontiguousarray(x, dtype=np.float64) for x in (ws_lb, ws_ub)]
+    mk = [np.ascontiguousarray(x, dtype=np.uint8) for x in (cand, s_cand, deads)]
+    new = np.zeros(net.N, dtype=np.uint8); merged = np.zeros(net.N, dtype=np.uint8)
+    lib().fo_heuristic_prune(net.L, _p(net.dims), _p(a[0]), _p(a[1]), _p(mk[0]), _p(mk[1]), _p(mk[2]),
+                             C.c_double(pct), _p(new), _p(merged))
+    return new, merged
+
+
+def pair_screen(net, X, pa_cols, alts):
+    X = np.ascontiguousarray(X, dtype=np.float32); m = X.shape[0]
+    pa = np.ascontiguousarray(pa_cols, dtype=np.int32)
+    alts = np.ascontiguousarray(alts, dtype=np.float32).reshape(-1, len(pa))
+    orig = np.zeros(m, dtype=np.uint8); flip = np.zeros(m, dtype=np.int32)
+    lib().fo_pair_screen(net.L, _p(net.dims), _p(net.W32), _p(net.B32), C.c_int64(m), _p(X), len(pa), _p(pa),
+                         alts.shape[0], _p(alts), _p(orig), _p(flip))
+    return orig, flip
+
+
+def partition_screen(net, samples, boxes, pa_col):
+    samples = np.ascontiguousarray(samples, dtype=np.int32); boxes = np.ascontiguousarray(boxes, dtype=np.int32)
+    n, S = samples.shape[0], samples.shape[1]
+    outs = [np.zeros(n, dtype=np.int32) for _ in range(3)]
+    lib().fo_partition_screen(net.L, _p(net.dims), _p(net.W32), _p(net.B32), C.c_int64(n), S, _p(samples),
+                              _p(boxes), int(pa_col), *[_p(o) for o in outs])
+    return outs
+
+
+def prune_batch(net, boxes, seed, first_index, S, tol):
+    boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
+    tol = np.ascontiguousarray(tol, dtype=np.float64)
+    counts = np.zeros((n, net.N), dtype=np.uint32)
+    names = ("cand", "b_dead", "dead", "sliver")
+    outs = {k: np.zeros((n, net.N), dtype=np.uint8) for k in names}
+    verdict = np.zeros(n, dtype=np.uint8)
+    lib().fo_prune_batch(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), _p(boxes), C.c_uint64(seed),
+                         C.c_int64(first_index), S, _p(tol), _p(counts), *[_p(outs[k]) for k in names], _p(verdict))
+    outs["counts"] = counts; outs["verdict"] = verdict
+    return outs
+
+
+def num_threads():
+    return int(lib().fo_num_threads())
+
+
+def sliver_tolerance(net, lo, hi):
+    """Per-neuron bound on |float ws_ub - exact ws_ub| valid for every box inside [lo, hi].
+
+    Standard recursive-summation bound: (in+1) roundings of relative size 2^-53 on terms whose
+    magnitudes sum to at most M_j = sum_i |w_ij| * max|x_i| + |b_j|, with a x4 safety factor.  The same
+    formula is used by the host library (fairify_b200.engine.sliver_tolerance); kept separately here so
+    the oracle stays self-contained.
+    """
+    mag = np.maximum(np.abs(np.asarray(lo, dtype=np.float64)), np.abs(np.asarray(hi, dtype=np.float64)))
+    tol = np.zeros(net.N)
+    wo = 0
+    for l in range(net.L):
+        i, o = int(net.dims[l]), int(net.dims[l + 1])
+        w = np.abs(net.W[wo:wo + i * o].reshape(i, o)); wo += i * o
+        b = np.abs(net.B[net.boff[l]:net.boff[l + 1]])
+        M = mag @ w + b
+        tol[net.boff[l]:net.boff[l + 1]] = 4.0 * (i + 2) * 2.0 ** -53 * M
+        mag = M
+    return tol

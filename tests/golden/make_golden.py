@@ -1,0 +1,281 @@
+#!/usr/bin/env python3
+"""Generate the committed golden fixtures by running the UNMODIFIED reference in the build container.
+
+    python tests/golden/make_golden.py            # writes tests/golden/*.npz  (needs /root/reference)
+
+What it runs (reference file:line):
+  * utils/input_partition.py:17-76  partition + partitioned_ranges  -> grid checksums / sampled boxes
+  * utils/prune.py:205-222          simluate_data (after np.random.seed(k))
+  * utils/prune.py:168-192          candidate_dead_nodes with utils/<M>-Model-Functions.py layer_net
+  * utils/prune.py:105-164          neuron_bounds   (weights pre-cast to float64: the float64 semantics of
+                                    the reference's pinned numpy 1.19; numpy >= 2 would otherwise keep
+                                    float32 products)
+  * utils/prune.py:226-251          dead_node_from_bound, :941-948 merge_dead_nodes, :194-203 compression_ratio
+  * utils/prune.py:671-783          sound_prune / sound_prune_german / sound_prune_bank INCLUDING the Z3
+                                    singular_verification, on a few small models
+  * utils/prune.py:862-939          heuristic_prune
+  * utils/<M>-Model-Functions.py    net (float64 on integer rows, float32 on float32 rows)
+  * src/AC/metrics.py:40-264        CausalDiscriminationDetector with a numpy float32 predict function
+Weights come from models/*/*.h5 through fairify_b200/h5weights.py (no tensorflow / h5py here).
+The fixtures hold inputs by seed (the sample matrix is regenerated with the stream-identical
+np.random.randint(lo, hi+1, size=(S, d)) and verified here against simluate_data) and outputs by value.
+"""
+import glob
+import hashlib
+import os
+import sys
+
+import numpy as np
+import pandas as pd
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.abspath(os.path.join(HERE, "..", ".."))
+
+# load this repo's pure-data helpers WITHOUT importing its `utils` package
+import importlib.util
+
+
+def _load(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+h5weights = _load(os.path.join(ROOT, "fairify_b200", "h5weights.py"), "h5weights")
+domains = _load(os.path.join(ROOT, "fairify_b200", "domains.py"), "domains")
+refshim = _load(os.path.join(ROOT, "oracle", "refshim.py"), "refshim")
+
+REF = refshim.REFERENCE_ROOT
+MODEL_DIRS = {"AC": "adult", "GC": "german", "BM": "bank", "CP": "compass", "DF": "default"}
+# second, finer partition threshold per domain for the prune cases (grid sizes 67 392 / 2 001 / 6 300 / 4)
+FINER_T = {"AC": 8, "GC": 30, "BM": 40, "CP": 10}
+
+
+def flat(lists):
+    return np.concatenate([np.asarray(l, dtype=np.float64).ravel() for l in lists])
+
+
+def flat_u8(lists):
+    return np.concatenate([np.asarray(l, dtype=np.uint8).ravel() for l in lists])
+
+
+def box_array(p, columns):
+    return np.array([[p[c][0], p[c][1]] for c in columns], dtype=np.int32)
+
+
+def write_weights():
+    out = {}
+    for f in sorted(glob.glob(os.path.join(REF, "models", "*", "*.h5"))):
+        name = os.path.basename(f)[:-3]
+        w, b = h5weights.read_keras_dense_weights(f)
+        out[f"{name}/L"] = np.int32(len(w))
+        for l, (wl, bl) in enumerate(zip(w, b)):
+            out[f"{name}/w{l}"] = wl
+            out[f"{name}/b{l}"] = bl
+    np.savez_compressed(os.path.join(HERE, "weights.npz"), **out)
+    print("weights.npz:", len([k for k in out if k.endswith('/L')]), "models")
+    return out
+
+
+def grids(ref):
+    out = {}
+    cases = [
+        ("AC_T10", "AC", 10, {}), ("GC_T100", "GC", 100, {}), ("BM_T100", "BM", 100, {}),
+        ("GC_T10", "GC", 10, {}), ("CP_T5", "CP", 5, {}),
+        ("AC_T6_age30_35", "AC", 6, {"age": [30, 35]}),              # targeted/AC/Verify-AC.py:33
+        ("GC_T10_purpose7", "GC", 10, {"purpose": [7, 7]}),          # targeted GC
+        ("BM_T10_small", "BM", 10, {"duration": [0, 95], "pdays": [0, 40]}),
+    ]
+    for tag, dom, T, override in cases:
+        D = domains.DOMAINS[dom]
+        rd = D.copy_ranges()
+        for k, v in override.items():
+            rd[k] = list(v)
+        p_dict = ref.input_partition.partition(rd, T)
+        p_list = ref.input_partition.partitioned_ranges(rd.keys(), D.pa, p_dict, rd)
+        boxes = np.stack([box_array(p, D.columns) for p in p_list])
+        out[f"{tag}/n"] = np.int64(len(p_list))
+        out[f"{tag}/sha256"] = np.frombuffer(hashlib.sha256(boxes.tobytes()).digest(), dtype=np.uint8)
+        idx = np.unique(np.concatenate([np.arange(min(4, len(p_list))),
+                                        np.linspace(0, len(p_list) - 1, 9).astype(np.int64)]))
+        out[f"{tag}/idx"] = idx
+        out[f"{tag}/boxes"] = boxes[idx]
+        out[f"{tag}/T"] = np.int64(T)
+        out[f"{tag}/lo"] = np.array([rd[c][0] for c in D.columns], dtype=np.int64)
+        out[f"{tag}/hi"] = np.array([rd[c][1] for c in D.columns], dtype=np.int64)
+        out[f"{tag}/key_order"] = np.array([D.columns.index(k) for k in rd.keys()], dtype=np.int32)
+        print(f"grid {tag}: n={len(p_list)}")
+    np.savez_compressed(os.path.join(HERE, "grids.npz"), **out)
+
+
+def prune_cases(ref, weights):
+    P = ref.prune
+    out = {}
+    models = (["GC-%d" % i for i in range(1, 6)] + ["AC-%d" % i for i in range(1, 13)]
+              + ["BM-%d" % i for i in range(1, 9)] + ["CP-1"])
+    full_z3 = {"GC-3", "GC-4", "AC-1", "AC-8", "BM-6"}
+    sound = {"AC": P.sound_prune, "GC": P.sound_prune_german, "BM": P.sound_prune_bank, "CP": P.sound_prune_compass}
+    case_id = 0
+    for name in models:
+        dom = name.split("-")[0]
+        D = domains.DOMAINS[dom]
+        L = int(weights[f"{name}/L"])
+        w32 = [weights[f"{name}/w{l}"] for l in range(L)]
+        b32 = [weights[f"{name}/b{l}"] for l in range(L)]
+        w64 = [x.astype(np.float64) for x in w32]
+        b64 = [x.astype(np.float64) for x in b32]
+        layer_net, net = refshim.model_functions(name)
+        df = pd.DataFrame(np.zeros((2, D.d + 1)), columns=D.columns + [D.label])
+        x_df = df.drop(labels=[D.label], axis=1)
+        rd = D.copy_ranges()
+        # two grids per domain: the src/ threshold and a finer one
+        plist = []
+        for T in (D.threshold, FINER_T[dom]):
+            p_dict = ref.input_partition.partition(rd, T)
+            pl = ref.input_partition.partitioned_ranges(rd.keys(), D.pa, p_dict, rd)
+            sel = sorted(set([0, 1, len(pl) // 3, len(pl) // 2, len(pl) - 1]))
+            plist += [pl[i] for i in sel]
+        big = sum(x.size for x in w32) > 4000
+        if big:
+            plist = plist[:4]
+        for k, p in enumerate(plist):
+            S = 1000 if k % 3 == 0 else 200
+            seed = 1000 + case_id
+            tag = f"{name}/{k}"
+            np.random.seed(seed)
+            with refshim.quiet():
+                sim_df = P.simluate_data(x_df, S, p)
+            sim = sim_df.to_numpy()
+            # the vectorised draw the tests use must be stream-identical to the scalar loop
+            np.random.seed(seed)
+            lo = np.array([p[c][0] for c in D.columns]); hi = np.array([p[c][1] for c in D.columns])
+            vec = np.random.randint(lo, hi + 1, size=(S, D.d))
+            assert np.array_equal(vec, sim), "vectorised randint is not stream-identical"
+            with refshim.quiet():
+                cand, pos_prob = P.candidate_dead_nodes(sim, w64, b64, layer_net)
+                ws_lb, ws_ub, pl_lb, pl_ub = P.neuron_bounds(sim_df, w64, b64, p)
+                b_dead, b_cand, b_ratio = P.dead_node_from_bound(cand, w64, b64, p, ws_ub)
+            for l in b_dead:
+                if 0 not in l:
+                    l[0] = 0
+            assert isinstance(ws_ub[0][0], (float, np.float64))
+            out[f"{tag}/seed"] = np.int64(seed); out[f"{tag}/S"] = np.int64(S)
+            out[f"{tag}/box"] = box_array(p, D.columns)
+            out[f"{tag}/sim_sha256"] = np.frombuffer(hashlib.sha256(sim.astype(np.int32).tobytes()).digest(), dtype=np.uint8)
+            out[f"{tag}/cand"] = flat_u8(cand); out[f"{tag}/pos_prob"] = flat(pos_prob)
+            out[f"{tag}/ws_lb"] = flat(ws_lb); out[f"{tag}/ws_ub"] = flat(ws_ub)
+            out[f"{tag}/pl_lb"] = flat(pl_lb); out[f"{tag}/pl_ub"] = flat(pl_ub)
+            out[f"{tag}/b_dead"] = flat_u8(b_dead); out[f"{tag}/b_cand"] = flat_u8(b_cand)
+            out[f"{tag}/b_compression"] = np.float64(P.compression_ratio(b_dead))
+            # heuristic prune on the bound-only masks (s_candidates == b_candidates when Z3 finds nothing)
+            with refshim.quiet():
+                merged0 = P.merge_dead_nodes(b_dead, [[0] * len(l) for l in b_dead])
+            for pct in (5, 20, 50, 100):
+                with refshim.quiet():
+                    nd, md = P.heuristic_prune((ws_lb, ws_ub, pl_lb, pl_ub), cand, b_cand, merged0, pos_prob, pct, w64, b64)
+                out[f"{tag}/h{pct}_new"] = flat_u8(nd); out[f"{tag}/h{pct}_merged"] = flat_u8(md)
+            # logits: float64 on the integer sample rows, float32 on float32 rows with float32 weights
+            rows = sim[:64]
+            out[f"{tag}/logit64"] = np.array([float(net(r, w64, b64)[0]) for r in rows])
+            l32 = [net(r.astype(np.float32), w32, b32)[0] for r in rows]
+            assert all(isinstance(v, np.float32) for v in l32)
+            out[f"{tag}/logit32"] = np.array(l32, dtype=np.float32)
+            if name in full_z3 and k < 3:
+                np.random.seed(seed)
+                with refshim.quiet():
+                    (bounds, c2, s_cand, bd2, s_dead, dead, pp2, sdf2) = sound[dom](df, w64, b64, S, layer_net, p)
+                assert np.array_equal(sdf2.to_numpy(), sim) and c2 == cand and bd2 == b_dead
+                out[f"{tag}/s_cand"] = flat_u8(s_cand); out[f"{tag}/s_dead"] = flat_u8(s_dead)
+                out[f"{tag}/dead"] = flat_u8(dead)
+                out[f"{tag}/st_compression"] = np.float64(P.compression_ratio(dead))
+                out[f"{tag}/s_compression"] = np.float64(P.compression_ratio(s_dead))
+            case_id += 1
+        out[f"{name}/ncases"] = np.int64(len(plist))
+        print(f"prune cases {name}: {len(plist)}")
+    out["models"] = np.array(models)
+    np.savez_compressed(os.path.join(HERE, "prune_cases.npz"), **out)
+
+
+def np_stats():
+    """numpy mean / median / percentile on random float64 vectors (heuristic_prune's statistics)."""
+    rng = np.random.RandomState(7)
+    out = {}
+    lens = list(range(1, 41)) + [63, 64, 65, 100, 127, 128, 129, 130, 137, 150, 200, 301]
+    vecs, res = [], []
+    for n in lens:
+        v = rng.standard_normal(n) * 10.0 ** rng.randint(-3, 4)
+        vecs.append(v)
+        row = [np.mean(v), np.median(v)]
+        for pct in (0, 5, 20, 50, 80, 95, 100):
+            row.append(np.percentile(v, pct))
+        res.append(row)
+    out["lens"] = np.array(lens); out["data"] = np.concatenate(vecs); out["res"] = np.array(res)
+    out["numpy_version"] = np.array(np.__version__)
+    np.savez_compressed(os.path.join(HERE, "np_stats.npz"), **out)
+
+
+def causal_cases(weights):
+    M = refshim.metrics_module("AC")
+    out = {}
+
+    def make_predict(name, columns):
+        L = int(weights[f"{name}/L"])
+        w = [weights[f"{name}/w{l}"] for l in range(L)]
+        b = [weights[f"{name}/b{l}"] for l in range(L)]
+        stats = {"min_abs": np.inf}
+
+        def predict(fd):
+            # the shape of model_predict_fn_original, src/AC/metrics.py:323-325, with the Dense stack in numpy float32
+            x = np.array([[fd[f] for f in columns]], dtype=np.float32)
+            for l in range(L):
+                x = x @ w[l] + b[l]
+                if l < L - 1:
+                    x = np.maximum(x, np.float32(0))
+            stats["min_abs"] = min(stats["min_abs"], float(abs(x[0][0])))
+            sig = np.float32(1) / (np.float32(1) + np.exp(-x[0][0], dtype=np.float32))
+            return int(sig > 0.5)
+        return predict, stats
+
+    cases = [("AC-1", "AC", ["sex"], 0.999, 0.0001), ("AC-3", "AC", ["race"], 0.99, 0.01),
+             ("GC-1", "GC", ["age"], 0.999, 0.0001), ("BM-1", "BM", ["age"], 0.99, 0.02),
+             ("AC-1", "AC", ["race", "sex"], 0.95, 0.02), ("GC-4", "GC", ["sex", "age"], 0.999, 0.0001)]
+    for ci, (name, dom, pa, conf, margin) in enumerate(cases):
+        D = domains.DOMAINS[dom]
+        predict, stats = make_predict(name, D.columns)
+        det = M.CausalDiscriminationDetector(predict, max_samples=1000, min_samples=100)
+        for c in D.columns:
+            lo, hi = D.ranges[c]
+            vals = list(range(lo, hi + 1))
+            if len(vals) > 60:                       # keep value lists dataset-like
+                vals = vals[::max(1, len(vals) // 40)]
+            det.add_feature(c, vals)
+        test_cases, rate, pairs = det.causal_discrimination(pa, conf=conf, margin=margin)
+        tag = f"case{ci}"
+        out[f"{tag}/model"] = np.array(name); out[f"{tag}/pa"] = np.array(pa)
+        out[f"{tag}/conf"] = np.float64(conf); out[f"{tag}/margin"] = np.float64(margin)
+        out[f"{tag}/rate"] = np.float64(rate)
+        out[f"{tag}/test_cases"] = np.array([[float(tc[c]) for c in D.columns] for tc in test_cases], dtype=np.float32)
+        out[f"{tag}/pairs"] = np.array([[[float(a[c]) for c in D.columns], [float(b_[c]) for c in D.columns]]
+                                        for a, b_ in pairs], dtype=np.float32).reshape(-1, 2, D.d)
+        out[f"{tag}/min_abs_logit"] = np.float64(stats["min_abs"])
+        for c in D.columns:
+            out[f"{tag}/values/{c}"] = np.array([float(v) for v in det.inputs[c].values], dtype=np.float32)
+        print(f"causal {name} {pa}: rate={rate:.4f} cases={len(test_cases)} pairs={len(pairs)} min|logit|={stats['min_abs']:.3g}")
+    out["ncases"] = np.int64(len(cases))
+    np.savez_compressed(os.path.join(HERE, "causal_cases.npz"), **out)
+
+
+def main():
+    if not refshim.available():
+        sys.exit("reference checkout not found; fixtures can only be regenerated in the build container")
+    ref = refshim.load()
+    weights = write_weights()
+    grids(ref)
+    np_stats()
+    prune_cases(ref, weights)
+    causal_cases(weights)
+
+
+if __name__ == "__main__":
+    main()

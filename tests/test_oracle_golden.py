@@ -1,0 +1,143 @@
+"""CPU: the oracle (oracle/fairify_oracle.c) against the golden vectors the UNMODIFIED reference produced
+(tests/golden/make_golden.py).  This is what pins the oracle; the GPU tests then compare against it."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests.common import Golden
+
+G = Golden()
+MODELS = G.models
+
+
+@pytest.mark.parametrize("tag", ["AC_T10", "GC_T100", "BM_T100", "GC_T10", "CP_T5", "AC_T6_age30_35",
+                                 "GC_T10_purpose7", "BM_T10_small"])
+def test_grid_matches_reference(tag):
+    """partition + partitioned_ranges (utils/input_partition.py:17-76): count, every box (sha256), sampled boxes."""
+    g = G.grids
+    lo, hi, T, ko = g[f"{tag}/lo"], g[f"{tag}/hi"], int(g[f"{tag}/T"]), g[f"{tag}/key_order"]
+    n, _ = O.grid_count(lo, hi, T)
+    assert n == int(g[f"{tag}/n"])
+    boxes = O.grid_boxes(lo, hi, T, ko, 0, n)
+    assert hashlib.sha256(boxes.tobytes()).digest() == g[f"{tag}/sha256"].tobytes()
+    for k, idx in enumerate(g[f"{tag}/idx"]):
+        assert np.array_equal(O.grid_boxes(lo, hi, T, ko, int(idx), 1)[0], g[f"{tag}/boxes"][k])
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_bounds_bit_exact(name):
+    """neuron_bounds (utils/prune.py:105-164): all four bound arrays bit-for-bit."""
+    net = O.Net(*G.wb(name))
+    for c in G.cases(name):
+        ws_lb, ws_ub, pl_lb, pl_ub = O.ibp(net, c["box"][None])
+        for got, key in ((ws_lb, "ws_lb"), (ws_ub, "ws_ub"), (pl_lb, "pl_lb"), (pl_ub, "pl_ub")):
+            assert np.array_equal(got[0], c[key]), f"{c['tag']} {key}"
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_directed_bounds_enclose_reference(name):
+    """outward-rounded enclosure contains the reference bounds and is within 1e-9 relative of them."""
+    net = O.Net(*G.wb(name))
+    for c in G.cases(name):
+        lb_rd, ub_ru = O.ibp_directed(net, c["box"][None])
+        assert np.all(lb_rd[0] <= c["ws_lb"]) and np.all(ub_ru[0] >= c["ws_ub"]), c["tag"]
+        scale = np.maximum(1.0, np.maximum(np.abs(c["ws_lb"]), np.abs(c["ws_ub"])))
+        assert np.all((c["ws_lb"] - lb_rd[0]) <= 1e-9 * scale) and np.all((ub_ru[0] - c["ws_ub"]) <= 1e-9 * scale)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_profile_and_masks(name):
+    """candidate_dead_nodes (:168-192), dead_node_from_bound (:226-251) + keep-one fix, compression_ratio."""
+    net = O.Net(*G.wb(name))
+    dom = G.domain(name)
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    tol = O.sliver_tolerance(net, lo, hi)
+    for c in G.cases(name):
+        counts = O.profile(net, c["samples"][None])
+        S = int(c["S"])
+        assert np.array_equal(counts[0] == 0, c["cand"].astype(bool)), c["tag"]
+        assert np.array_equal(counts[0] / S, c["pos_prob"]), c["tag"]
+        ws_ub = O.ibp(net, c["box"][None])[1]
+        m = O.masks(net, counts, ws_ub, tol)
+        assert np.array_equal(m["cand"][0], c["cand"])
+        assert np.array_equal(m["b_dead"][0], c["b_dead"]), c["tag"]
+        assert np.array_equal(m["b_cand"][0], c["b_cand"]), c["tag"]
+        assert O.compression_ratio(m["b_dead"][0]) == float(c["b_compression"])
+        assert not m["sliver"].any()
+        if "dead" in c:       # full sound_prune* run including the Z3 singular_verification
+            assert np.array_equal(m["s_dead"][0], c["s_dead"]), c["tag"]
+            assert np.array_equal(m["dead"][0], c["dead"]), c["tag"]
+            assert np.array_equal(m["b_cand"][0], c["s_cand"]), c["tag"]
+            assert O.compression_ratio(m["dead"][0]) == float(c["st_compression"])
+            assert float(c["s_compression"]) == 0.0
+
+
+def test_known_answers_from_the_reference_notebook():
+    """reproduce.ipynb: B_compression plateaus at 0.7 (GC-3) and 0.6364 (GC-4) on the src/GC grid."""
+    vals = {}
+    for name in ("GC-3", "GC-4"):
+        vals[name] = [round(float(c["b_compression"]), 4) for c in G.cases(name)]
+    assert 0.7 in vals["GC-3"] and 0.6364 in vals["GC-4"]
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_heuristic_prune(name):
+    """heuristic_prune (:862-939) for the thresholds the drivers use (5, 20, 50, 100)."""
+    net = O.Net(*G.wb(name))
+    for c in G.cases(name):
+        for pct in (5, 20, 50, 100):
+            new, merged = O.heuristic_prune(net, c["ws_lb"], c["ws_ub"], c["cand"], c["b_cand"], c["b_dead"], pct)
+            assert np.array_equal(new, c[f"h{pct}_new"]), f"{c['tag']} pct={pct}"
+            assert np.array_equal(merged, c[f"h{pct}_merged"]), f"{c['tag']} pct={pct}"
+
+
+def test_numpy_statistics_restatement():
+    """np.mean / np.median / np.percentile as restated in C, bit-exact on random vectors of many lengths."""
+    import ctypes as C
+    s = G.stats
+    lib = O.lib()
+    off = 0
+    for n, want in zip(s["lens"], s["res"]):
+        v = np.ascontiguousarray(s["data"][off:off + n]); off += n
+        srt = np.sort(v)
+        p = v.ctypes.data_as(C.c_void_p); ps = srt.ctypes.data_as(C.c_void_p)
+        got = [lib.fo_np_mean(p, int(n)), lib.fo_np_median_sorted(ps, int(n))]
+        for pct in (0, 5, 20, 50, 80, 95, 100):
+            got.append(lib.fo_np_percentile_sorted(ps, int(n), C.c_double(pct)))
+        assert np.array_equal(np.array(got), want), f"n={n}"
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_logits(name):
+    """net (utils/<M>-Model-Functions.py): sign always, value to 1e-12 (f64) / 1e-5 (f32) relative --
+    the reference sums through BLAS in an unspecified order, the oracle in index order."""
+    net = O.Net(*G.wb(name))
+    for c in G.cases(name):
+        rows = c["samples"][:64]
+        y64 = O.forward_f64(net, rows.astype(np.float64))
+        y32 = O.forward_f32(net, rows.astype(np.float32))
+        assert np.array_equal(y64 > 0, c["logit64"] > 0) and np.array_equal(y32 > 0, c["logit32"] > 0)
+        assert np.allclose(y64, c["logit64"], rtol=1e-12, atol=1e-12)
+        assert np.allclose(y32, c["logit32"], rtol=1e-4, atol=1e-4)
+
+
+def test_philox_reference_vector():
+    """Philox4x32-10 known-answer test (Random123 kat_vectors: counter = key = 0 and all-ones)."""
+    import ctypes as C
+    # exercised through fo_philox_samples: range 2^31 on feature 0..3 exposes the raw words' top bits
+    boxes = np.array([[[0, 2 ** 31 - 1]] * 4], dtype=np.int32)
+    s = O.philox_samples(0, 0, boxes, 1)[0, 0]
+    want = np.array([0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8], dtype=np.uint64) >> np.uint64(1)
+    assert np.array_equal(s.astype(np.uint64), want)
+
+
+def test_philox_samples_in_range_and_uniform():
+    boxes = np.array([[[10, 19], [0, 0], [-3, 1], [0, 20000], [5, 6]]], dtype=np.int32)
+    s = O.philox_samples(1234, 7, boxes, 4000)[0]
+    assert np.all(s >= boxes[0, :, 0]) and np.all(s <= boxes[0, :, 1])
+    for i in (0, 2, 4):
+        vals, cnt = np.unique(s[:, i], return_counts=True)
+        assert len(vals) == boxes[0, i, 1] - boxes[0, i, 0] + 1
+        assert cnt.min() > 0.7 * 4000 / len(vals)
