@@ -221,9 +221,10 @@ extern "C" int64_t fb_grid_size(const fb_grid *g) { return g ? g->n : -1; }
 
 extern "C" int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int32_t *boxes, void *stream)
 {
-    if (!g || !boxes) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: null argument");
+    if (!g) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: null grid");
     if (first < 0 || count < 0 || first + count > g->n) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: range [%lld, %lld) outside the grid of %lld", (long long)first, (long long)(first + count), (long long)g->n);
     if (count == 0) return FB_OK;
+    if (!boxes) return fb_fail(FB_ERR_INVALID, "fb_grid_boxes: null output");
     int sms = 0;
     if (fb_num_sms(&sms)) return FB_ERR_CUDA;
     const int grid = (int)std::min<int64_t>((count + 255) / 256, (int64_t)sms * 8);

@@ -1,0 +1,318 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the reference's golden vectors.
+
+Bar: bit-exact for masks, counts, verdicts, grid boxes, samples and the round-to-nearest bounds;
+the outward-rounded bounds must contain the reference bounds and stay within 1e-9 relative of them."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import oracle as O  # noqa: E402
+from tests.common import Golden  # noqa: E402
+
+G = Golden()
+MODELS = G.models
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from fairify_b200 import engine
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return engine
+
+
+def _tol(eng, name):
+    dom = G.domain(name)
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    w, b = G.wb(name)
+    return eng.sliver_tolerance(w, b, lo, hi)
+
+
+def test_library_loaded_and_native(eng):
+    from fairify_b200 import _lib
+    assert _lib.lib().fb_version() >= 100
+    m = eng.Model(*G.wb("AC-1"))
+    assert m.specialised and m.N == 25 and m.P == 344
+
+
+@pytest.mark.parametrize("tag", ["AC_T10", "GC_T100", "BM_T100", "GC_T10", "CP_T5", "AC_T6_age30_35",
+                                 "GC_T10_purpose7", "BM_T10_small"])
+def test_grid_boxes_match_reference(eng, tag):
+    from fairify_b200.domains import DOMAINS
+    g = G.grids
+    dom = DOMAINS[tag.split("_")[0]]
+    rd = dom.copy_ranges()
+    lo, hi = g[f"{tag}/lo"], g[f"{tag}/hi"]
+    for c, a, b in zip(dom.columns, lo, hi):
+        rd[c] = [int(a), int(b)]
+    grid = eng.Grid(dom.columns, rd, int(g[f"{tag}/T"]))
+    assert len(grid) == int(g[f"{tag}/n"])
+    boxes = grid.boxes().cpu().numpy()
+    assert hashlib.sha256(boxes.tobytes()).digest() == g[f"{tag}/sha256"].tobytes()
+    # ragged windows: a slice in the middle and the empty slice
+    mid = grid.boxes(len(grid) // 3, min(5, len(grid) - len(grid) // 3)).cpu().numpy()
+    assert np.array_equal(mid, boxes[len(grid) // 3: len(grid) // 3 + mid.shape[0]])
+    assert grid.boxes(0, 0).shape[0] == 0
+    with pytest.raises(Exception):
+        grid.boxes(len(grid) - 1, 2)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_prune_matches_reference_goldens(eng, name):
+    """sound_prune* outputs on the reference's own samples (injected), all golden cases of the model."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b)
+    tol = _tol(eng, name)
+    by_S = {}
+    for c in G.cases(name):
+        by_S.setdefault(int(c["S"]), []).append(c)
+    for S, cs in by_S.items():
+        boxes = np.stack([c["box"] for c in cs]); samples = np.stack([c["samples"] for c in cs])
+        r = m.prune(boxes, samples=samples, tol=tol, want=eng.ALL_OUTPUTS)
+        cand, b_dead, dead, sliver = r.bits("cand"), r.bits("b_dead"), r.bits("dead"), r.bits("sliver")
+        counts = r.numpy("counts").view(np.uint16)
+        for k, c in enumerate(cs):
+            assert np.array_equal(cand[k], c["cand"]), c["tag"]
+            assert np.array_equal(counts[k] / S, c["pos_prob"]), c["tag"]
+            assert np.array_equal(b_dead[k], c["b_dead"]), c["tag"]
+            assert not sliver[k].any()
+            if "dead" in c:
+                assert np.array_equal(dead[k], c["dead"]), c["tag"]
+            else:
+                assert np.array_equal(dead[k], c["b_dead"]), c["tag"]
+            for key in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"):
+                assert np.array_equal(r.numpy(key)[k], c[key]), f"{c['tag']} {key}"
+            lb_rd, ub_ru = r.numpy("lb_rd")[k], r.numpy("ub_ru")[k]
+            assert np.all(lb_rd <= c["ws_lb"]) and np.all(ub_ru >= c["ws_ub"]), c["tag"]
+            scale = np.maximum(1.0, np.maximum(np.abs(c["ws_lb"]), np.abs(c["ws_ub"])))
+            assert np.all(c["ws_lb"] - lb_rd <= 1e-9 * scale) and np.all(ub_ru - c["ws_ub"] <= 1e-9 * scale)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_prune_matches_oracle_philox(eng, name):
+    """device-drawn samples: counts, masks, verdict and both bound chains against the oracle, bit for bit."""
+    from fairify_b200.domains import STRESS_THRESHOLD
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    T = STRESS_THRESHOLD.get(dom.name, dom.threshold)
+    grid = eng.Grid(dom.columns, dom.ranges, T)
+    big = m.P > 4000
+    n = 24 if big else 96
+    first = max(0, len(grid) // 2 - 7)
+    n = min(n, len(grid) - first)
+    S = 100 if big else 333                      # ragged: not a multiple of 32
+    boxes = grid.boxes(first, n)
+    hb = boxes.cpu().numpy()
+    tol = _tol(eng, name)
+    r = m.prune(boxes, S=S, seed=99, first_index=first, tol=tol, want=eng.ALL_OUTPUTS)
+    want = O.prune_batch(net, hb, 99, first, S, tol)
+    assert np.array_equal(r.numpy("counts").view(np.uint16), want["counts"].astype(np.uint16))
+    assert np.array_equal(r.bits("cand"), want["cand"])
+    assert np.array_equal(r.bits("b_dead"), want["b_dead"])
+    assert np.array_equal(r.bits("dead"), want["dead"])
+    assert np.array_equal(r.bits("sliver"), want["sliver"])
+    assert np.array_equal(r.numpy("verdict"), want["verdict"])
+    o_rn = O.ibp(net, hb); o_dir = O.ibp_directed(net, hb)
+    for key, ref in zip(("ws_lb", "ws_ub", "pl_lb", "pl_ub"), o_rn):
+        assert np.array_equal(r.numpy(key), ref), key
+    assert np.array_equal(r.numpy("lb_rd"), o_dir[0]) and np.array_equal(r.numpy("ub_ru"), o_dir[1])
+
+
+@pytest.mark.parametrize("name", ["AC-1", "GC-1", "BM-4"])
+def test_profile_few_partitions_uses_sample_chunks(eng, name):
+    """with very few partitions the samples are split over several warps and merged atomically."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    grid = eng.Grid(dom.columns, dom.ranges, dom.threshold)
+    boxes = grid.boxes(0, 3)
+    counts = m.profile(boxes, S=1000, seed=5, first_index=0).cpu().numpy()
+    samples = O.philox_samples(5, 0, boxes.cpu().numpy(), 1000)
+    assert np.array_equal(counts.astype(np.uint32), O.profile(net, samples))
+    # injected copy of the same samples must give the same counts
+    counts2 = m.profile(boxes, samples=samples).cpu().numpy()
+    assert np.array_equal(counts, counts2)
+
+
+@pytest.mark.parametrize("name", ["AC-1", "AC-12", "GC-2", "BM-1"])
+def test_generic_kernels_agree_with_specialised(eng, name):
+    """FAIRIFY_B200_FORCE_GENERIC routes a specialised shape through the runtime-shape kernels (subprocess)."""
+    import subprocess
+    import sys
+    code = f"""
+import numpy as np, sys
+sys.path.insert(0, {os.path.dirname(os.path.dirname(os.path.abspath(__file__)))!r})
+from tests.common import Golden
+from fairify_b200 import engine
+from oracle import oracle as O
+G = Golden(); w, b = G.wb({name!r}); m = engine.Model(w, b); net = O.Net(w, b)
+dom = G.domain({name!r}); grid = engine.Grid(dom.columns, dom.ranges, dom.threshold)
+n = min(40, len(grid)); boxes = grid.boxes(0, n); hb = boxes.cpu().numpy()
+lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+tol = engine.sliver_tolerance(w, b, lo, hi)
+r = m.prune(boxes, S=77, seed=3, tol=tol, want=engine.ALL_OUTPUTS)
+want = O.prune_batch(net, hb, 3, 0, 77, tol)
+assert np.array_equal(r.numpy('counts').view(np.uint16), want['counts'].astype(np.uint16))
+assert np.array_equal(r.bits('b_dead'), want['b_dead']) and np.array_equal(r.numpy('verdict'), want['verdict'])
+assert np.array_equal(r.numpy('ws_ub'), O.ibp(net, hb)[1]) and np.array_equal(r.numpy('ub_ru'), O.ibp_directed(net, hb)[1])
+X = O.philox_samples(3, 0, hb, 8).reshape(-1, m.d)
+assert np.array_equal(m.forward(X.astype(np.float64)).cpu().numpy(), O.forward_f64(net, X))
+assert np.array_equal(m.forward(X.astype(np.float32)).cpu().numpy(), O.forward_f32(net, X))
+print('generic-ok', m.specialised)
+"""
+    env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "generic-ok" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_forward_logits(eng, name):
+    """net: float64 on integer rows, float32 on float32 rows; bit-exact vs the oracle, sign-exact vs numpy."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    for c in list(G.cases(name))[:3]:
+        rows = c["samples"][:64]
+        y64 = m.forward(rows.astype(np.float64)).cpu().numpy()
+        y32 = m.forward(rows.astype(np.float32)).cpu().numpy()
+        assert np.array_equal(y64, O.forward_f64(net, rows)) and np.array_equal(y32, O.forward_f32(net, rows))
+        assert np.array_equal(y64 > 0, c["logit64"] > 0) and np.array_equal(y32 > 0, c["logit32"] > 0)
+        assert np.allclose(y64, c["logit64"], rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", ["AC-1", "GC-1", "AC-4", "BM-8"])
+def test_forward_with_dead_mask_equals_pruned_network(eng, name):
+    """zeroing dead activations == prune_neurons' column/row deletion (utils/prune.py:950-977)."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b)
+    c = next(iter(G.cases(name)))
+    dead = c["b_dead"].astype(bool)
+    layers = m.split(dead)
+    pw, pb = [x.copy() for x in w], [x.copy() for x in b]
+    for l in range(m.L):
+        keep = ~layers[l]
+        pw[l] = pw[l][:, keep]; pb[l] = pb[l][keep]
+        if l + 1 < m.L:
+            pw[l + 1] = pw[l + 1][keep, :]
+    rows = c["samples"][:128].astype(np.float64)
+    y_masked = m.forward(rows, dead_bits=eng.pack_bits(c["b_dead"][None])[0]).cpu().numpy()
+    y_pruned = eng.Model(pw, pb).forward(rows).cpu().numpy()
+    assert np.array_equal(y_masked, y_pruned)
+    # sound pruning never changes a prediction on the partition's own samples ('Pruned-acc' == 1.0)
+    assert np.array_equal(y_masked > 0, m.forward(rows).cpu().numpy() > 0)
+
+
+@pytest.mark.parametrize("ci", range(6))
+def test_pair_screen_matches_reference_detector(eng, ci):
+    """CausalDiscriminationDetector.causal_discrimination (src/AC/metrics.py:101-168): rate, test cases and
+    causal pairs reproduced from device predictions + the host replay of the sampler and stopping rule."""
+    from fairify_b200.screen import causal_discrimination
+    from fairify_b200.domains import domain_for_model
+    z = G.causal
+    name = str(z[f"case{ci}/model"]); pa = [str(x) for x in z[f"case{ci}/pa"]]
+    dom = domain_for_model(name)
+    m = eng.Model(*G.wb(name))
+    values = {c: [float(v) for v in z[f"case{ci}/values/{c}"]] for c in dom.columns}
+    test_cases, rate, pairs = causal_discrimination(m, dom.columns, values, pa, conf=float(z[f"case{ci}/conf"]),
+                                                    margin=float(z[f"case{ci}/margin"]))
+    assert rate == float(z[f"case{ci}/rate"])
+    assert np.array_equal(np.asarray(test_cases, dtype=np.float32), z[f"case{ci}/test_cases"])
+    assert np.array_equal(np.asarray(pairs, dtype=np.float32).reshape(-1, 2, dom.d), z[f"case{ci}/pairs"])
+
+
+@pytest.mark.parametrize("name", ["AC-1", "AC-3", "GC-1", "GC-4", "BM-5", "AC-5"])
+def test_partition_screen_matches_oracle(eng, name):
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    grid = eng.Grid(dom.columns, dom.ranges, dom.threshold)
+    n = min(200, len(grid))
+    boxes = grid.boxes(0, n); hb = boxes.cpu().numpy()
+    for pa_name in (dom.pa[0], dom.columns[0]):
+        pa_col = dom.columns.index(pa_name)
+        S = 150
+        verdict = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        ce, vp, vn = [t.cpu().numpy() for t in m.partition_screen(boxes, pa_col, S=S, seed=11, verdict=verdict)]
+        samples = O.philox_samples(11, 0, hb, S)
+        oce, ovp, ovn = O.partition_screen(net, samples, hb, pa_col)
+        assert np.array_equal(ce, oce) and np.array_equal(vp, ovp) and np.array_equal(vn, ovn)
+        assert np.array_equal(verdict.cpu().numpy() == 2, oce >= 0)
+        # injected samples give the same answer
+        ce2, vp2, vn2 = [t.cpu().numpy() for t in m.partition_screen(boxes, pa_col, samples=samples)]
+        assert np.array_equal(ce2, oce) and np.array_equal(vp2, ovp) and np.array_equal(vn2, ovn)
+        # every reported counterexample really flips the float32 class
+        for p in np.nonzero(oce >= 0)[0][:20]:
+            x = samples[p, oce[p]].astype(np.float32)
+            xa, xb = x.copy(), x.copy(); xa[pa_col] = ovp[p]; xb[pa_col] = ovn[p]
+            ya, yb = O.forward_f32(net, np.stack([xa, xb]))
+            assert ya > 0 and yb < 0
+
+
+def test_prune_host_roundtrip_equals_device(eng):
+    w, b = G.wb("AC-1")
+    m = eng.Model(w, b)
+    dom = G.domain("AC-1")
+    grid = eng.Grid(dom.columns, dom.ranges, 10)
+    boxes = grid.boxes(100, 5000)
+    tol = _tol(eng, "AC-1")
+    r = m.prune(boxes, S=64, seed=7, first_index=100, tol=tol)
+    hb = boxes.cpu().pin_memory()
+    out = m.prune_host(hb, S=64, seed=7, first_index=100, tol=tol)
+    for k in ("cand", "b_dead", "dead", "sliver", "verdict", "counts"):
+        assert np.array_equal(out[k].numpy(), r.numpy(k)), k
+
+
+def test_empty_batch_and_bad_arguments(eng):
+    w, b = G.wb("GC-3")
+    m = eng.Model(w, b)
+    r = m.prune(np.zeros((0, m.d, 2), dtype=np.int32), S=10)
+    assert r.numpy("verdict").shape == (0,)
+    with pytest.raises(Exception):
+        m.prune(np.zeros((1, m.d, 2), dtype=np.int32), S=0)
+    with pytest.raises(Exception):
+        eng.Model([np.zeros((3, 2), np.float32)], [np.zeros(2, np.float32)])      # two logits
+    with pytest.raises(Exception):
+        eng.Model([np.full((3, 1), np.nan, np.float32)], [np.zeros(1, np.float32)])
+
+
+def test_full_size_properties(eng):
+    """At a size the oracle cannot finish quickly: size-independent properties of the 16 000-box src/AC grid,
+    S = 1000.  (i) a bound-dead neuron is never seen active (soundness of the interval test),
+    (ii) outward bounds enclose the nearest ones, (iii) certified partitions have no sampled counterexample,
+    (iv) sharding invariance: any split of the index range gives the same bytes."""
+    w, b = G.wb("AC-1")
+    m = eng.Model(w, b)
+    dom = G.domain("AC-1")
+    grid = eng.Grid(dom.columns, dom.ranges, 10)
+    boxes = grid.boxes()
+    tol = _tol(eng, "AC-1")
+    r = m.prune(boxes, S=1000, seed=2024, tol=tol, want=eng.ALL_OUTPUTS)
+    counts = r.numpy("counts").view(np.uint16)
+    b_dead, cand = r.bits("b_dead").astype(bool), r.bits("cand").astype(bool)
+    assert np.all(counts[b_dead] == 0) and np.array_equal(cand, counts == 0)
+    assert np.all(r.numpy("lb_rd") <= r.numpy("ws_lb")) and np.all(r.numpy("ub_ru") >= r.numpy("ws_ub"))
+    assert np.all(counts[:, -1] == 1000)            # the logit is never exactly 0
+    le0 = r.numpy("ws_ub") <= 0
+    expect = cand & le0
+    expect[:, -1] = cand[:, -1]
+    for l in range(m.L):                            # keep-one fix, utils/prune.py:689-691
+        sl = slice(int(m.boff[l]), int(m.boff[l + 1]))
+        alldead = expect[:, sl].all(axis=1)
+        expect[alldead, int(m.boff[l])] = False
+    assert np.array_equal(b_dead, expect)
+    pa_col = dom.columns.index("sex")
+    verdict = r.t["verdict"].clone()
+    ce = m.partition_screen(boxes, pa_col, S=1000, seed=2024, verdict=verdict)[0].cpu().numpy()
+    v = verdict.cpu().numpy()
+    assert not np.any((v & 1).astype(bool) & (ce >= 0))
+    # sharding invariance (what the multi-GPU path relies on)
+    cut = 7001
+    r1 = m.prune(boxes[:cut], S=1000, seed=2024, first_index=0, tol=tol)
+    r2 = m.prune(boxes[cut:], S=1000, seed=2024, first_index=cut, tol=tol)
+    for k in ("cand", "b_dead", "verdict", "counts"):
+        assert np.array_equal(np.concatenate([r1.numpy(k), r2.numpy(k)]), r.numpy(k)), k
