@@ -15,7 +15,7 @@ SO_PATH = os.path.join(_HERE, "libfairify_b200.so")
 EXPORTS = [
     "fb_version", "fb_last_error", "fb_num_sms", "fb_model_create", "fb_model_destroy", "fb_model_info",
     "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_profile", "fb_ibp", "fb_prune",
-    "fb_prune_host", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_fp64_peak",
+    "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_fp64_peak",
 ]
 
 
@@ -56,6 +56,7 @@ def lib():
     L.fb_ibp.argtypes = [vp, i64, vp, vp, vp, C.POINTER(PruneOut), vp]
     L.fb_prune.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, C.POINTER(PruneOut), vp]
     L.fb_prune_host.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, C.POINTER(PruneOut), vp]
+    L.fb_prune_noalloc.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, C.POINTER(PruneOut), vp]
     L.fb_forward_f64.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_forward_f32.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_pair_screen.argtypes = [vp, i64, vp, i32, vp, i32, vp, vp, vp, vp]

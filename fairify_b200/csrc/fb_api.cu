@@ -36,6 +36,8 @@ static int fb_fail(int code, const char *fmt, ...)
     } while (0)
 
 extern "C" const char *fb_last_error(void) { return fb_err; }
+// for the library's other translation units (not part of the C ABI)
+void fb_set_error(const char *msg) { snprintf(fb_err, sizeof(fb_err), "%s", msg); }
 extern "C" int fb_version(void) { return 100; }
 
 extern "C" int fb_num_sms(int *out)

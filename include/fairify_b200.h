@@ -96,6 +96,18 @@ int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *
 int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
                   int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
 
+/* -- fb_prune for callers that must not allocate.  (No counterpart in the reference, which never manages
+ *    device memory; it exists for embedders of this library.)  Same arguments, results and error
+ *    convention as fb_prune, but the [n][N] uint32 count scratch is a fixed 16 MiB array inside the library
+ *    image instead of a per-call allocation, so the call issues no cudaMalloc / cudaFree of any kind.
+ *    Meant for hosts that forbid device allocation after start-up (allocator locks stall other streams),
+ *    that have already carved up all of HBM, or that account every allocation themselves.
+ *    Limits: n * N <= 4 194 304 (FB_ERR_UNSUPPORTED beyond that; e.g. 167 772 partitions for AC-1).
+ *    The first call on each device resolves the array's address; make it at start-up, before any stream
+ *    capture.  All calls on a device share the one array: calls that overlap on the GPU race. */
+int fb_prune_noalloc(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                     int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
+
 /* -- logits: `net`, utils/<MODEL>-Model-Functions.py (e.g. AC-1 :25-32); get_y_pred utils/verif_utils.py:1040-1047.
  *    dead_bits [NW] or NULL: neurons forced to 0 (== the pruned network of prune_neurons, utils/prune.py:950-977). */
 int fb_forward_f64(const fb_model *m, int64_t rows, const double *X, const uint32_t *dead_bits, double *logits, void *stream);
