@@ -116,6 +116,7 @@ def cpu_rate(target_seconds, fixed_sample=None):
     """evals/s of the oracle port on all host threads, on a bounded slice of the same workload."""
     from oracle import oracle as O
     from fairify_b200.domains import DOMAINS
+    O.set_threads(len(os.sched_getaffinity(0)))        # all host threads, whatever OMP_NUM_THREADS torchrun exported
     w, b = load_ac1()
     net = O.Net(w, b)
     D = DOMAINS["AC"]
@@ -167,6 +168,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     from fairify_b200 import engine
+    from fairify_b200.dist import pack_records
     from fairify_b200.domains import DOMAINS
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -222,9 +224,7 @@ def run_gpu(args):
         if timers:
             timers[2].record()
         if world > 1:
-            packed[:, 0] = outs["verdict"]
-            packed[:, 1:1 + NW] = outs["dead"]
-            packed[:, 1 + NW:] = outs["cand"]
+            pack_records(outs["verdict"], outs["dead"], outs["cand"], out=packed)
             dist.all_gather_into_tensor(gathered, packed)
 
     for _ in range(args.warmup):

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libfairify_b200.so")
+SO_PATH = os.environ.get("FAIRIFY_B200_LIB") or os.path.join(_HERE, "libfairify_b200.so")
 
 # every symbol include/fairify_b200.h declares
 EXPORTS = [

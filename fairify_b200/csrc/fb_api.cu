@@ -242,13 +242,14 @@ extern "C" int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int
 // the machine with one warp each.
 static void fb_pick_chunks(const fb_model *m, int64_t n, int S, int *chunks, int *chunk_len)
 {
-    const int max_len = FB_PROFILE_MAX_STEPS * 32;
+    const int max_len = FB_PROFILE_MAX_STEPS * 32 * FB_PROFILE_SPT;
     const int64_t want_warps = (int64_t)m->num_sms * 64;
     int c = 1;
-    if (n < want_warps) c = (int)std::min<int64_t>((S + 31) / 32, (want_warps + n - 1) / n);
+    const int gran = 32 * FB_PROFILE_SPT;       // samples one warp step covers in the specialised kernel
+    if (n < want_warps) c = (int)std::min<int64_t>((S + gran - 1) / gran, (want_warps + n - 1) / n);
     c = std::max(c, (S + max_len - 1) / max_len);
     int len = (S + c - 1) / c;
-    len = ((len + 31) / 32) * 32;
+    len = ((len + gran - 1) / gran) * gran;
     c = (S + len - 1) / len;
     *chunks = std::max(c, 1); *chunk_len = len;
 }

@@ -12,22 +12,22 @@
 // Visit::neuron(idx, last, pre) returns the activation fed to the next layer; idx and last fold to
 // constants because every call site is inside fully unrolled loops.
 // ---------------------------------------------------------------------------------------------------
-template <class S, int l, typename T, class Visit>
-__device__ __forceinline__ T fb_spec_forward(const SpecParams<S, T> &prm, const T (&x)[S::dim(l)], Visit &v)
+template <class S, int l, typename T, class PRM, class Visit>
+__device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
 {
     constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
     constexpr bool last = (l == S::NL - 1);
     T y[OUT];
 #pragma unroll
     for (int j = 0; j < OUT; ++j) {
-        T acc = (T)0;
+        T acc = T(0.0);
 #pragma unroll
         for (int i = 0; i < IN; ++i) acc = fb_fma(prm.w[WO + i * OUT + j], x[i], acc);
         const T pre = fb_add(acc, prm.b[BO + j]);
         y[j] = v.neuron(BO + j, last, pre);
     }
     if constexpr (last) return y[0];
-    else return fb_spec_forward<S, l + 1, T, Visit>(prm, y, v);
+    else return fb_spec_forward<S, l + 1, T, PRM, Visit>(prm, y, v);
 }
 
 // plain ReLU visitor (logit only)
@@ -49,32 +49,160 @@ struct FbMaskedVisit {
     }
 };
 
-// activation-profile visitor: per-lane packed 8-bit counters, one field per neuron.
-// reference: candidate_dead_nodes, utils/prune.py:175-180 (activation != 0, output layer included)
-template <int N>
+// ---------------------------------------------------------------------------------------------------
+// Activation profile.  reference: candidate_dead_nodes, utils/prune.py:168-192 (activation != 0 counted per
+// neuron, output layer included) over the samples of simluate_data (:205-222).
+//
+// One warp per (partition, sample chunk).  Each lane carries K = FB_PROFILE_SPT samples per step, so a step
+// covers 32*K samples.  The forward pass is input-major: acc[j] += w[i][j] * x_i for i ascending -- per
+// output neuron the terms are added in exactly the order of fb_spec_forward / the oracle -- which lets one
+// uniform constant-bank fetch of a weight feed K fused multiply-adds, and lets layer 0 take each feature
+// from a generator right where it is consumed (a sample's 13..30 features never sit in registers together).
+// ---------------------------------------------------------------------------------------------------
+#define FB_PROFILE_THREADS 128
+#ifndef FB_PROFILE_SPT
+#define FB_PROFILE_SPT 2                                 // samples per lane per step
+#endif
+#ifndef FB_PROFILE_IM
+#define FB_PROFILE_IM 0                                  // 1: input-major forward, 0: output-major (measured best)
+#endif
+#ifndef FB_PROFILE_MINB
+#define FB_PROFILE_MINB 4                                // minimum resident CTAs per SM (caps registers at 128)
+#endif
+#define FB_PROFILE_MAX_STEPS (255 / FB_PROFILE_SPT)      // per-lane counters are 8-bit fields
+
+// per-lane packed 8-bit counters, one field per neuron
+template <int N, int K>
 struct FbCountVisit {
-    uint32_t cnt[(N + 3) / 4];
-    bool active;
-    __device__ __forceinline__ double neuron(int idx, bool last, double pre)
+    uint32_t (&cnt)[(N + 3) / 4];
+    bool active[K];             // false for sample slots past the end of the chunk (ragged last step)
+    __device__ __forceinline__ VecD<K> neuron(int idx, bool last, const VecD<K> &pre)
     {
-        const bool nz = last ? fb_nonzero(pre) : fb_pos(pre);
-        if (nz && active) cnt[idx >> 2] += 1u << (8 * (idx & 3));
-        return last ? pre : (fb_pos(pre) ? pre : 0.0);
+        VecD<K> r;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const bool pos = fb_pos(pre.v[k]);
+            const bool nz = last ? fb_nonzero(pre.v[k]) : pos;
+            if (nz && active[k]) cnt[idx >> 2] += 1u << (8 * (idx & 3));
+            r.v[k] = last ? pre.v[k] : (pos ? pre.v[k] : 0.0);
+        }
+        return r;
     }
 };
 
-#define FB_PROFILE_THREADS 128
-#define FB_PROFILE_MAX_STEPS 255     // 8-bit per-lane counters
+template <class S, int l, typename T, class PRM, class Visit>
+__device__ __forceinline__ void fb_spec_layer_epilogue(const PRM &prm, T (&y)[S::dim(l + 1)], Visit &v)
+{
+    constexpr int OUT = S::dim(l + 1), BO = S::boff(l);
+    constexpr bool last = (l == S::NL - 1);
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) y[j] = v.neuron(BO + j, last, fb_add(y[j], prm.b[BO + j]));
+}
 
-// One warp per (partition, sample chunk); lanes are samples.
+template <class S, int l, typename T, class PRM, class Visit>
+__device__ __forceinline__ T fb_spec_forward_im(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
+{
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l);
+    T y[OUT];
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) y[j] = T(0.0);
+#pragma unroll
+    for (int i = 0; i < IN; ++i) {
+#pragma unroll
+        for (int j = 0; j < OUT; ++j) y[j] = fb_fma(prm.w[WO + i * OUT + j], x[i], y[j]);
+    }
+    fb_spec_layer_epilogue<S, l, T>(prm, y, v);
+    if constexpr (l == S::NL - 1) return y[0];
+    else return fb_spec_forward_im<S, l + 1, T, PRM, Visit>(prm, y, v);
+}
+
+template <class S, typename T, class PRM, class Visit, class XGen>
+__device__ __forceinline__ T fb_spec_forward_gen_in(const PRM &prm, XGen &xg, Visit &v)
+{
+    constexpr int IN = S::dim(0), OUT = S::dim(1);
+    T y[OUT];
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) y[j] = T(0.0);
+#pragma unroll
+    for (int i = 0; i < IN; ++i) {
+        const T xi = xg.feature(i);
+#pragma unroll
+        for (int j = 0; j < OUT; ++j) y[j] = fb_fma(prm.w[i * OUT + j], xi, y[j]);
+    }
+    fb_spec_layer_epilogue<S, 0, T>(prm, y, v);
+    if constexpr (S::NL == 1) return y[0];
+    else return fb_spec_forward_im<S, 1, T, PRM, Visit>(prm, y, v);
+}
+
+// layer-0 input generators: feature(i) is called for i = 0, 1, ... in order
+template <int D0, int K>
+struct FbPhiloxGen {
+    const int32_t (&lo)[D0];
+    const uint32_t (&range)[D0];
+    int s;                      // this lane's first sample of the step; its k-th sample is s + 32*k
+    int64_t pidx;
+    uint64_t seed;
+    uint32_t r[K][4];
+    __device__ __forceinline__ VecD<K> feature(int i)
+    {
+        if ((i & 3) == 0) {
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+                fb_philox4x32_10((uint32_t)(s + 32 * k), (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32),
+                                 (uint32_t)(i >> 2), (uint32_t)seed, (uint32_t)(seed >> 32), r[k]);
+        }
+        VecD<K> x;
+#pragma unroll
+        for (int k = 0; k < K; ++k) x.v[k] = (double)fb_map_range(r[k][i & 3], lo[i], range[i]);
+        return x;
+    }
+};
+
+template <int D0, int K>
+struct FbInjectGen {
+    const int32_t *row[K];
+    __device__ __forceinline__ VecD<K> feature(int i)
+    {
+        VecD<K> x;
+#pragma unroll
+        for (int k = 0; k < K; ++k) x.v[k] = (double)__ldg(row[k] + i);
+        return x;
+    }
+};
+
+// one step of the profile: this lane's K samples (indices s, s+32, ...) through the whole network
+template <class S, int K, bool PHILOX, class Visit>
+__device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm, Visit &vis, const int32_t (&lo)[S::D0],
+                                                const uint32_t (&range)[S::D0], const int32_t *part_samples, int s,
+                                                int64_t pidx, uint64_t seed, int s_clamp = 0x7fffffff)
+{
+    constexpr int D0 = S::D0;
+    if (PHILOX) {
+        FbPhiloxGen<D0, K> xg{lo, range, s, pidx, seed};
+#if FB_PROFILE_IM
+        fb_spec_forward_gen_in<S, VecD<K>>(prm, xg, vis);
+#else
+        VecD<K> x[D0];
+#pragma unroll
+        for (int i = 0; i < D0; ++i) x[i] = xg.feature(i);
+        fb_spec_forward<S, 0, VecD<K>>(prm, x, vis);
+#endif
+    } else {
+        FbInjectGen<D0, K> xg;
+#pragma unroll
+        for (int k = 0; k < K; ++k) xg.row[k] = part_samples + (int64_t)min(s + 32 * k, s_clamp) * D0;
+        fb_spec_forward_gen_in<S, VecD<K>>(prm, xg, vis);
+    }
+}
+
 // counts[p][N] (uint32): stored when chunks == 1, atomically added otherwise (caller zeroes first).
 template <class S, bool PHILOX>
-__global__ void __launch_bounds__(FB_PROFILE_THREADS)
+__global__ void __launch_bounds__(FB_PROFILE_THREADS, FB_PROFILE_MINB)
 fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
                        const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
                        int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *__restrict__ counts)
 {
-    constexpr int D0 = S::D0, N = S::N;
+    constexpr int D0 = S::D0, N = S::N, K = FB_PROFILE_SPT;
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -94,35 +222,24 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
                 lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
             }
         }
-        FbCountVisit<N> vis;
+        uint32_t cnt[(N + 3) / 4];
 #pragma unroll
-        for (int k = 0; k < (N + 3) / 4; ++k) vis.cnt[k] = 0;
+        for (int k = 0; k < (N + 3) / 4; ++k) cnt[k] = 0;
         const int64_t pidx = first_index + p;
-        for (int sb = s0; sb < s1; sb += 32) {
-            const int s = sb + lane;
-            vis.active = s < s1;
-            double x[D0];
-            if (PHILOX) {
+        // one copy of the unrolled network: the ragged last step is handled by the per-sample activity flags
+        // (a second, flag-free copy for the full steps doubles the code and loses more in instruction fetch
+        // than the flags cost)
+        for (int sb = s0; sb < s1; sb += 32 * K) {
+            FbCountVisit<N, K> vis{cnt};
 #pragma unroll
-                for (int blk = 0; blk * 4 < D0; ++blk) {
-                    uint32_t r[4];
-                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
-                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (blk * 4 + k < D0) x[blk * 4 + k] = (double)fb_map_range(r[k], lo[blk * 4 + k], range[blk * 4 + k]);
-                }
-            } else {
-                const int32_t *row = samples + ((int64_t)p * nsamp + (vis.active ? s : s0)) * D0;
-#pragma unroll
-                for (int i = 0; i < D0; ++i) x[i] = (double)__ldg(row + i);
-            }
-            fb_spec_forward<S, 0, double>(prm, x, vis);
+            for (int k = 0; k < K; ++k) vis.active[k] = (sb + 32 * k + lane) < s1;
+            fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
+                                          s1 - 1);
         }
         uint32_t mine = 0;
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-            const uint32_t tot = __reduce_add_sync(0xffffffffu, (vis.cnt[j >> 2] >> (8 * (j & 3))) & 0xffu);
+            const uint32_t tot = __reduce_add_sync(0xffffffffu, (cnt[j >> 2] >> (8 * (j & 3))) & 0xffu);
             if ((j & 31) == lane) mine = tot;
             if ((j & 31) == 31 || j == N - 1) {
                 const int jj = (j & ~31) + lane;

@@ -55,6 +55,15 @@ static int fo_net_init(fo_net *m, int L, const int32_t *dims, const double *W, c
     return 0;
 }
 
+void fo_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int fo_num_threads(void)
 {
 #ifdef _OPENMP

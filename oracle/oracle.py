@@ -176,6 +176,11 @@ def num_threads():
     return int(lib().fo_num_threads())
 
 
+def set_threads(n):
+    """Use n OpenMP threads from now on (torchrun exports OMP_NUM_THREADS=1, which would hide the host's cores)."""
+    lib().fo_set_threads(int(n))
+
+
 def sliver_tolerance(net, lo, hi):
     """Per-neuron bound on |float ws_ub - exact ws_ub| valid for every box inside [lo, hi].
 
