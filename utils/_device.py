@@ -1,0 +1,51 @@
+"""Model cache and thin helpers between the reference-shaped API and fairify_b200.engine."""
+import hashlib
+
+import numpy as np
+
+from fairify_b200 import engine
+
+_models = {}
+
+
+def model_for(w, b):
+    """engine.Model for these weights (cached by content: the drivers pass freshly pruned arrays each time)."""
+    h = hashlib.blake2b(digest_size=16)
+    for a in list(w) + list(b):
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        h.update(str(a.shape).encode()); h.update(a.tobytes())
+    key = h.digest()
+    m = _models.get(key)
+    if m is None:
+        if len(_models) > 64:
+            _models.clear()
+        m = engine.Model([np.asarray(x, dtype=np.float32) for x in w], [np.asarray(x, dtype=np.float32) for x in b])
+        _models[key] = m
+    return m
+
+
+def logits(X, w, b):
+    """numpy logits for rows X: float32 when both X and the weights are float32 (numpy's promotion in
+    `w.T @ x`), float64 otherwise."""
+    X = np.asarray(X)
+    f32 = X.dtype == np.float32 and all(np.asarray(a).dtype == np.float32 for a in w)
+    m = model_for(w, b)
+    out = m.forward(X.astype(np.float32 if f32 else np.float64))
+    return out.cpu().numpy()
+
+
+def layer_activations(x, w, b):
+    """Per-layer activations of one input.  Only the interactive `layer_net` call needs them; they are the
+    device bounds of the degenerate box [x, x] (lower == upper == the pre-activation)."""
+    x = np.asarray(x)
+    if np.issubdtype(x.dtype, np.integer):
+        m = model_for(w, b)
+        box = np.stack([x, x], axis=1).astype(np.int32)[None]
+        # degenerate box: lower == upper == W^T x + b summed in the reference order of neuron_bounds
+        r = m.ibp(box, want=("ws_lb",))
+        pre = r.numpy("ws_lb")[0]
+        acts = m.split(np.where(pre > 0, pre, 0.0))
+        acts[-1] = m.split(pre)[-1]
+        return [np.array(a) for a in acts]
+    raise TypeError("layer_net is only defined for integer sample rows on the GPU path "
+                    "(the reference calls it from candidate_dead_nodes alone, utils/prune.py:169,176)")

@@ -1,0 +1,292 @@
+"""Drop-in for the reference's utils/prune.py, with the pre-solver stage on the GPU.
+
+Same function names, positional signatures and return structures as the reference (plain lists of lists, a
+pandas `sim_df`), so `from utils.prune import *` keeps the unchanged drivers working:
+
+    bounds, candidates, s_candidates, b_deads, s_deads, st_deads, pos_prob, sim_X_df = \
+        sound_prune(df, w, b, simulation_size, layer_net, p)              # src/AC/Verify-AC.py:117-118
+
+What runs where
+  * sampling keeps the reference's RNG: `np.random.randint(lo, hi+1, size=(S, d))` consumes the global legacy
+    stream exactly like the scalar loop of `simluate_data` (utils/prune.py:205-222) -- same seed, same samples;
+  * activation profile, interval bounds, masks, keep-one fixes, merge: one `fb_prune` call on the device
+    (`candidate_dead_nodes` :168-192, `neuron_bounds` :105-164, `dead_node_from_bound` :226-251, :689-705);
+  * the per-neuron Z3 query (`singular_verification*`, :276-644) stays on the host.  It asks whether
+    y_j > 0 is satisfiable over the layer's input box; the device already knows the supremum of y_j over that
+    box (it is ws_ub), so the query is only run for neurons whose bound is within rounding error of zero
+    ("slivers").  FAIRIFY_GPU_SINGULAR=reference runs it for every remaining candidate like the reference,
+    =off never runs it.  s_dead is all-zero in every published result and every fixture.
+  * `prune_neurons`, `compression_ratio`, `merge_dead_nodes`, `heuristic_prune` operate on a handful of
+    Python lists per partition and feed Z3; they stay host code.
+"""
+import copy
+import os
+
+import numpy as np
+import pandas as pd
+
+from utils import _device
+from utils.verif_utils import *  # noqa: F401,F403  (the reference's prune.py leaks these names to the drivers too)
+
+LABELS = {'adult': 'income-per-year', 'bank': 'y', 'german': 'credit', 'compass': 'score_factor',
+          'default': 'default.payment.next.month'}
+
+
+# ----------------------------------------------------------------------------------------------------
+# small host helpers (list-of-lists <-> flat arrays)
+# ----------------------------------------------------------------------------------------------------
+def _split_lists(model, flat, cast):
+    return [[cast(v) for v in part] for part in model.split(np.asarray(flat))]
+
+
+def _box_from(cols, range_dict):
+    return np.array([[range_dict[c][0], range_dict[c][1]] for c in cols], dtype=np.int32)
+
+
+def _keep_one(mask):
+    for l in mask:
+        if 0 not in l:
+            l[0] = 0
+    return mask
+
+
+# ----------------------------------------------------------------------------------------------------
+# reference API, piece by piece
+# ----------------------------------------------------------------------------------------------------
+def simluate_data(df, size, range_dict):
+    """`size` uniform integer rows inside the box (reference :205-222), drawn from the global numpy stream in
+    the same order as the reference's scalar loop."""
+    cols = df.columns.values
+    lo = np.array([range_dict[c][0] for c in cols]); hi = np.array([range_dict[c][1] for c in cols])
+    sim = np.random.randint(lo, hi + 1, size=(size, len(cols)))
+    return pd.DataFrame(data=sim, columns=cols)
+
+
+def candidate_dead_nodes(data, weight, bias, layer_net):
+    """(dead mask, positive_prob): neurons that are never non-zero on the samples (reference :168-192)."""
+    m = _device.model_for(weight, bias)
+    data = np.asarray(data)
+    samples = np.ascontiguousarray(data, dtype=np.int32)[None]
+    if not np.array_equal(samples[0], data):
+        raise TypeError("candidate_dead_nodes expects integer sample rows (it gets simluate_data's output)")
+    counts = m.profile(np.zeros((1, m.d, 2), dtype=np.int32), samples=samples).cpu().numpy()[0]
+    dead = _split_lists(m, (counts == 0).astype(np.int64), int)
+    prob = _split_lists(m, counts / data.shape[0], float)
+    return dead, prob
+
+
+def neuron_bounds(df, w, b, range_dict):
+    """(ws_lb, ws_ub, pl_lb, pl_ub) exactly as the reference's float64 recurrence computes them (:105-164)."""
+    m = _device.model_for(w, b)
+    box = _box_from(df.columns.values, range_dict)[None]
+    r = m.ibp(box, want=("ws_lb", "ws_ub", "pl_lb", "pl_ub"))
+    return tuple(_split_lists(m, r.numpy(k)[0], float) for k in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"))
+
+
+def dead_node_from_bound(cand, weight, bias, range_dict, ws_ub):
+    """Candidates whose upper bound is <= 0 are dead; last layer untouched (reference :226-251)."""
+    print('INTERVAL BASED PRUNING')
+    candidates = copy.deepcopy(cand)
+    dead = copy.deepcopy(cand)
+    finds = total = 0
+    for l in range(len(ws_ub) - 1):
+        for j in range(len(ws_ub[l])):
+            total += 1
+            if candidates[l][j] == 0:
+                continue
+            if ws_ub[l][j] <= 0:
+                finds += 1; dead[l][j] = 1; candidates[l][j] = 0
+            else:
+                dead[l][j] = 0
+    return dead, candidates, finds / total
+
+
+def compression_ratio(deads):
+    total = sum(len(l) for l in deads)
+    alive = sum(1 for l in deads for d in l if not d)
+    return 1 - (alive / total)
+
+
+def merge_dead_nodes(b, s):
+    merged = copy.deepcopy(b)
+    for l in range(len(s)):
+        for j in range(len(s[l])):
+            if s[l][j] == 1:
+                merged[l][j] = 1
+    return merged
+
+
+def prune_neurons(weight, bias, candidates):
+    """Delete dead columns / the next layer's rows (reference :950-977); feeds the Z3 encoder on the host."""
+    pr_w, pr_b = [], []
+    keep_prev = None
+    for i in range(len(weight)):
+        keep = ~np.asarray(candidates[i], dtype=bool)
+        wi = np.asarray(weight[i])
+        if keep_prev is not None:
+            wi = wi[keep_prev, :]
+        pr_w.append(wi[:, keep]); pr_b.append(np.asarray(bias[i])[keep])
+        keep_prev = keep
+    print('Pruning done!')
+    return pr_w, pr_b
+
+
+# ----------------------------------------------------------------------------------------------------
+# singular verification (host, Z3)
+# ----------------------------------------------------------------------------------------------------
+def _z3_positive_is_unsat(l, j, cols, weight, bias, ranges, pl_lb, pl_ub):
+    """The reference's query for one neuron: input-domain constraints + y_j > 0; True when unsat.
+    Layer 0 ranges over Int variables inside the box (:298-300); deeper layers over Real variables bounded by
+    pl_lb[l][k] <= x_k <= pl_ub[l][k] for k < len(pl_lb[l]) -- the reference indexes the post-activation
+    bounds with the layer's own index (:302-305, :266-273) and this restatement keeps that."""
+    import z3
+    W = np.asarray(weight[l], dtype=np.float64).astype(object)
+    B = np.asarray(bias[l], dtype=np.float64).astype(object)
+    if l == 0:
+        xi = [z3.Int('x%s' % i) for i in range(W.shape[0])]
+        props = [z3.And(xi[i] >= ranges[c][0], xi[i] <= ranges[c][1]) for i, c in enumerate(cols)]
+        x = np.array([z3.ToReal(v) for v in xi], dtype=object)
+    else:
+        x = np.array([z3.Real('x%s' % i) for i in range(W.shape[0])], dtype=object)
+        props = []
+        for k in range(len(pl_lb[l])):
+            props.append(x[k] >= pl_lb[l][k]); props.append(x[k] <= pl_ub[l][k])
+    y = W.T @ x + B
+    s = z3.Solver()
+    for p in props:
+        s.add(p)
+    s.add(y[j] > 0)
+    return s.check() == z3.unsat
+
+
+def _singular(cand, df, weight, bias, ranges, pl_lb, pl_ub, only=None):
+    print('SINGULAR VERIFICATION')
+    candidates = copy.deepcopy(cand)
+    dead = copy.deepcopy(cand)
+    cols = list(df.columns.values)
+    finds = total = 0
+    for l in range(len(candidates) - 1):
+        for j in range(len(candidates[l])):
+            total += 1
+            if candidates[l][j] == 0:
+                continue
+            run = only is None or only[l][j]
+            if run and _z3_positive_is_unsat(l, j, cols, weight, bias, ranges, pl_lb, pl_ub):
+                finds += 1; dead[l][j] = 1; candidates[l][j] = 0
+            else:
+                dead[l][j] = 0
+    return dead, candidates, (finds / total if total else 0.0)
+
+
+def singular_verification(cand, df, weight, bias, ranges, pl_lb, pl_ub):
+    return _singular(cand, df, weight, bias, ranges, pl_lb, pl_ub)
+
+
+singular_verification_german = singular_verification_bank = singular_verification
+singular_verification_compass = singular_verification_default = singular_verification
+
+
+# ----------------------------------------------------------------------------------------------------
+# sound_prune*: the drop-in entry points (reference :671-859; they differ only in the label column)
+# ----------------------------------------------------------------------------------------------------
+def _sound_prune(label_name, df, weight, bias, simulation_size, layer_net, range_dict):
+    x_df = df.drop(labels=[label_name], axis=1, inplace=False)
+    cols = x_df.columns.values
+    sim_df = simluate_data(x_df, simulation_size, range_dict)
+    m = _device.model_for(weight, bias)
+    box = _box_from(cols, range_dict)
+    tol = m.tolerance(box[:, 0], box[:, 1])
+    r = m.prune(box[None], samples=sim_df.to_numpy().astype(np.int32)[None], tol=tol,
+                want=("cand", "b_dead", "dead", "sliver", "verdict", "counts", "ws_lb", "ws_ub", "pl_lb", "pl_ub"))
+    bounds = tuple(_split_lists(m, r.numpy(k)[0], float) for k in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"))
+    counts = r.numpy("counts").view(np.uint16)[0]
+    cand_flat = r.bits("cand")[0]
+    candidates = _split_lists(m, cand_flat, int)
+    pos_prob = _split_lists(m, counts / simulation_size, float)
+    b_dead = _split_lists(m, r.bits("b_dead")[0], int)
+    print('INTERVAL BASED PRUNING')
+    # b_candidates: candidates not proven dead by the bound; last layer copied through (:235-251)
+    le0 = np.asarray(r.numpy("ws_ub")[0]) <= 0
+    b_cand_flat = cand_flat & ~le0
+    b_cand_flat[m.boff[m.L - 1]:] = cand_flat[m.boff[m.L - 1]:]
+    b_cand = _split_lists(m, b_cand_flat, int)
+
+    mode = os.environ.get("FAIRIFY_GPU_SINGULAR", "sliver")
+    sliver = _split_lists(m, r.bits("sliver")[0], int)
+    if mode == "reference":
+        s_dead, s_cand, _ = _singular(b_cand, x_df, weight, bias, range_dict, bounds[2], bounds[3])
+    elif mode != "off" and any(any(l) for l in sliver):
+        s_dead, s_cand, _ = _singular(b_cand, x_df, weight, bias, range_dict, bounds[2], bounds[3], only=sliver)
+    else:
+        print('SINGULAR VERIFICATION')
+        s_cand = copy.deepcopy(b_cand)
+        s_dead = [[0] * len(l) for l in b_cand]
+        s_dead[-1] = list(b_cand[-1])           # the reference copies the last layer through (:287-288)
+    _keep_one(s_dead)
+    dead_nodes = _keep_one(merge_dead_nodes(b_dead, s_dead))
+    return bounds, candidates, s_cand, b_dead, s_dead, dead_nodes, pos_prob, sim_df
+
+
+def sound_prune(df, weight, bias, simulation_size, layer_net, range_dict):
+    return _sound_prune(LABELS['adult'], df, weight, bias, simulation_size, layer_net, range_dict)
+
+
+def sound_prune_bank(df, weight, bias, simulation_size, layer_net, range_dict):
+    return _sound_prune(LABELS['bank'], df, weight, bias, simulation_size, layer_net, range_dict)
+
+
+def sound_prune_german(df, weight, bias, simulation_size, layer_net, range_dict):
+    return _sound_prune(LABELS['german'], df, weight, bias, simulation_size, layer_net, range_dict)
+
+
+def sound_prune_compass(df, weight, bias, simulation_size, layer_net, range_dict):
+    return _sound_prune(LABELS['compass'], df, weight, bias, simulation_size, layer_net, range_dict)
+
+
+def sound_prune_default(df, weight, bias, simulation_size, layer_net, range_dict):
+    return _sound_prune(LABELS['default'], df, weight, bias, simulation_size, layer_net, range_dict)
+
+
+def sound_prune_global(df, weight, bias, simulation_size, layer_net, range_dict):
+    """Reference :646-667: label = last column, returns the pruned weights."""
+    out = _sound_prune(df.columns[len(df.columns) - 1], df, weight, bias, simulation_size, layer_net, range_dict)
+    return prune_neurons(weight, bias, out[5])
+
+
+def harsh_prune(df, weight, bias, simulation_size, layer_net, range_dict):
+    """Reference :89-102: prune every sample-candidate (unsound), label = last column."""
+    x_data = df.drop(df.columns[len(df.columns) - 1], axis=1, inplace=False)
+    sim_df = simluate_data(x_data, simulation_size, range_dict)
+    candidates, _ = candidate_dead_nodes(sim_df.to_numpy(), weight, bias, layer_net)
+    print(candidates)
+    pr_w, pr_b = prune_neurons(weight, bias, candidates)
+    print(round(compression_ratio(candidates), 2), '% pruning')
+    return pr_w, pr_b
+
+
+# ----------------------------------------------------------------------------------------------------
+# heuristic_prune (reference :862-939): only reached after a Z3 `unknown`; a few numpy statistics per layer
+# ----------------------------------------------------------------------------------------------------
+def heuristic_prune(bounds, candidates, s_candidates, deads, pos_prob, perc_threshold, w, b):
+    ws_lb, ws_ub, pl_lb, pl_ub = bounds
+    new_deads = [[0] * len(l) for l in candidates]
+    for l in range(len(candidates) - 1):
+        cand = [ws_ub[l][j] for j in range(len(candidates[l])) if candidates[l][j]]
+        noncand = [ws_ub[l][j] for j in range(len(candidates[l])) if not candidates[l][j]]
+        if len(noncand) == 0:
+            for j in range(len(s_candidates[l])):
+                new_deads[l][j] = 1
+            continue
+        if len(cand) == 0:
+            continue
+        c, n = np.array(cand), np.array(noncand)
+        if np.mean(n) > 2 * np.mean(c) and np.median(n) > 2 * np.median(c):
+            low = np.percentile(n, perc_threshold)
+            high = np.percentile(n, 100 - perc_threshold)
+            for j in range(len(s_candidates[l])):
+                if s_candidates[l][j] and ws_ub[l][j] < low and ws_ub[l][j] < 0.1 * high \
+                        and ws_ub[l][j] < abs(ws_lb[l][j]):
+                    new_deads[l][j] = 1
+    _keep_one(new_deads)
+    merged = _keep_one(merge_dead_nodes(deads, new_deads))
+    return new_deads, merged

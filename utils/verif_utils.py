@@ -1,0 +1,90 @@
+"""Drop-in for the hot-path part of the reference's utils/verif_utils.py: `relu`, `sigmoid`, `get_y_pred`,
+`y_pred_mismatch` (reference :522-523, :1028-1033, :1040-1063) and the `load_model` the drivers reach through
+the star-import.  Predictions for a whole matrix are one kernel launch (`fb_forward_f64` / `_f32`) instead of
+one Python-level matrix product per row.  Everything else the reference module defines (Z3 property builders,
+dataset loaders) is host code that stays as it is and is re-exported from a reference checkout when present.
+"""
+import math
+import os    # noqa: F401  (the drivers rely on these leaking through `import *`, src/BM/Verify-BM.py:4-11)
+import time  # noqa: F401
+import copy  # noqa: F401
+import collections  # noqa: F401
+import datetime  # noqa: F401
+
+import numpy as np
+import pandas as pd  # noqa: F401
+from sklearn.metrics import accuracy_score, confusion_matrix, f1_score, roc_auc_score  # noqa: F401
+from sklearn.model_selection import train_test_split  # noqa: F401
+from sklearn.preprocessing import KBinsDiscretizer, LabelEncoder  # noqa: F401
+
+from utils import _device, _reference
+
+
+def relu(x):
+    return np.maximum(0, x)
+
+
+def sigmoid(x):
+    """Overflow-safe logistic (reference :1028-1033)."""
+    if x >= 0:
+        return 1 / (1 + math.exp(-x))
+    return math.exp(x) / (1 + math.exp(x))
+
+
+def _is_device_net(net):
+    return getattr(net, "__module__", "").endswith("-Model-Functions") or getattr(net, "__module__", "") == "utils._model_functions"
+
+
+def get_y_pred(net, w, b, X_test):
+    """[sigmoid(net(x)) > 0.5 for x in X_test] as a list of 1-element bool arrays (reference :1040-1047).
+    The logits come from one launch; the sigmoid/threshold is applied on the host with the reference's own
+    formula so that the boolean is identical even for logits within 1e-16 of zero."""
+    X = np.asarray(X_test)
+    if X.ndim == 1:
+        X = X[None, :]
+    if not _is_device_net(net):            # a foreign `net`: honour it, row by row, like the reference
+        return [np.asarray(sigmoid(net(x, w, b))) > 0.5 for x in X]
+    y = _device.logits(X, w, b)
+    return [np.array([sigmoid(v) > 0.5]) for v in y]
+
+
+def y_pred_mismatch(net, w, b, pr_w, pr_b, X_test, y_test):
+    """Print the rows on which the pruned and the original network disagree (reference :1049-1063)."""
+    a = get_y_pred(net, w, b, X_test); p = get_y_pred(net, pr_w, pr_b, X_test)
+    ya = _device.logits(np.asarray(X_test), w, b); yp = _device.logits(np.asarray(X_test), pr_w, pr_b)
+    for i in range(len(a)):
+        if a[i] != p[i]:
+            print('MISMATCH'); print(sigmoid(ya[i])); print(sigmoid(yp[i]))
+
+
+class _Layer:
+    def __init__(self, w, b):
+        self._w, self._b = w, b
+
+    def get_weights(self):
+        return [self._w, self._b]
+
+
+class _KerasLikeModel:
+    """What the drivers use of a keras model: `.layers[i].get_weights()` and `.predict(x)`."""
+
+    def __init__(self, w, b):
+        self.layers = [_Layer(wl, bl) for wl, bl in zip(w, b)]
+        self._w, self._b = w, b
+
+    def predict(self, x, verbose=0):
+        """float32 sigmoid outputs, shape (rows, 1): Dense stack in float32 on the device."""
+        y = _device.logits(np.asarray(x, dtype=np.float32).reshape(-1, self._w[0].shape[0]), self._w, self._b)
+        y = y.astype(np.float32)
+        return (np.float32(1) / (np.float32(1) + np.exp(-y, dtype=np.float32))).reshape(-1, 1)
+
+
+def load_model(path):
+    """Stand-in for tensorflow.keras.models.load_model: reads the Dense kernels/biases of a Fairify .h5 file."""
+    from fairify_b200.h5weights import read_keras_dense_weights
+    w, b = read_keras_dense_weights(path)
+    return _KerasLikeModel(w, b)
+
+
+# host-side names that are not on the GPU path: taken from the reference checkout when there is one
+_reference.reexport("verif_utils", globals(), skip=("load_model",))
