@@ -15,7 +15,7 @@ SO_PATH = os.environ.get("FAIRIFY_B200_LIB") or os.path.join(_HERE, "libfairify_
 EXPORTS = [
     "fb_version", "fb_last_error", "fb_num_sms", "fb_model_create", "fb_model_destroy", "fb_model_info",
     "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_profile", "fb_ibp", "fb_prune",
-    "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_fp64_peak",
+    "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_heuristic", "fb_fp64_peak",
 ]
 
 
@@ -61,6 +61,7 @@ def lib():
     L.fb_forward_f32.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_pair_screen.argtypes = [vp, i64, vp, i32, vp, i32, vp, vp, vp, vp]
     L.fb_partition_screen.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, vp, vp, vp, vp, vp]
+    L.fb_heuristic.argtypes = [vp, i64, vp, vp, vp, vp, vp, C.c_double, vp, vp, vp]
     L.fb_fp64_peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     _lib = L
     return L

@@ -511,6 +511,140 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
 }
 
 // ---------------------------------------------------------------------------------------------------
+// heuristic_prune (reference utils/prune.py:862-939), one partition per thread.  Runs only for partitions on
+// which Z3 answered `unknown`, so it is written for exactness, not speed: numpy's mean (pairwise sum with 8
+// accumulators per block of <= 128), median and linear-interpolated percentile are restated operation by
+// operation (same as oracle/fairify_oracle.c, which is checked bit for bit against numpy).
+// ---------------------------------------------------------------------------------------------------
+__device__ static double fb_np_pairwise_block(const double *a, int n)      // n <= 128
+{
+    if (n < 8) {
+        double r = 0.0;
+        for (int i = 0; i < n; ++i) r = __dadd_rn(r, a[i]);
+        return r;
+    }
+    double r[8];
+    int i;
+    for (i = 0; i < 8; ++i) r[i] = a[i];
+    for (i = 8; i < n - (n % 8); i += 8)
+        for (int k = 0; k < 8; ++k) r[k] = __dadd_rn(r[k], a[i + k]);
+    double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                           __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+    for (; i < n; ++i) res = __dadd_rn(res, a[i]);
+    return res;
+}
+// numpy splits blocks larger than 128 in two (recursively); layers are at most FB_MAXW <= 256 wide, so one
+// split suffices and no device recursion (and no dynamic stack) is needed
+__device__ static double fb_np_pairwise(const double *a, int n)
+{
+    static_assert(FB_MAXW <= 256, "fb_np_pairwise handles one level of numpy's pairwise split");
+    if (n <= 128) return fb_np_pairwise_block(a, n);
+    int n2 = n / 2;
+    n2 -= n2 % 8;
+    return __dadd_rn(fb_np_pairwise_block(a, n2), fb_np_pairwise_block(a + n2, n - n2));
+}
+__device__ static double fb_np_mean(const double *a, int n) { return __ddiv_rn(fb_np_pairwise(a, n), (double)n); }
+__device__ static void fb_insertion_sort(double *a, int n)
+{
+    for (int i = 1; i < n; ++i) {
+        const double v = a[i];
+        int k = i - 1;
+        while (k >= 0 && a[k] > v) { a[k + 1] = a[k]; --k; }
+        a[k + 1] = v;
+    }
+}
+__device__ static double fb_np_median_sorted(const double *s, int n)
+{
+    if (n & 1) return s[n / 2];
+    return __ddiv_rn(__dadd_rn(__dadd_rn(0.0, s[n / 2 - 1]), s[n / 2]), 2.0);
+}
+__device__ static double fb_np_percentile_sorted(const double *s, int n, double pct)
+{
+    const double q = __ddiv_rn(pct, 100.0);
+    const double v = __dmul_rn((double)(n - 1), q);
+    int prev, next;
+    double gamma;
+    if (v >= (double)(n - 1)) { prev = next = n - 1; gamma = __dadd_rn(v, -(double)(n - 1)); }
+    else if (v < 0) { prev = next = 0; gamma = v; }
+    else { prev = (int)floor(v); next = prev + 1; gamma = __dadd_rn(v, -(double)prev); }
+    const double a = s[prev], b = s[next], diff = __dadd_rn(b, -a);
+    double r = __dadd_rn(a, __dmul_rn(diff, gamma));
+    if (gamma >= 0.5) r = __dadd_rn(b, -__dmul_rn(diff, __dadd_rn(1.0, -gamma)));
+    return r;
+}
+
+__device__ static void fb_keep_one_bits(uint32_t *w, int bo, int out)
+{
+    for (int j = 0; j < out; ++j)
+        if (!((w[(bo + j) >> 5] >> ((bo + j) & 31)) & 1u)) return;
+    w[bo >> 5] &= ~(1u << (bo & 31));
+}
+
+__global__ void __launch_bounds__(64)
+fb_heuristic_kernel(const GenNet net, int64_t n, const double *__restrict__ ws_lb, const double *__restrict__ ws_ub,
+                    const uint32_t *__restrict__ cand, const uint32_t *__restrict__ s_cand,
+                    const uint32_t *__restrict__ deads, double pct, uint32_t *__restrict__ new_deads,
+                    uint32_t *__restrict__ merged)
+{
+    const int N = net.N, NW = (N + 31) / 32;
+    double cv[FB_MAXW], nv[FB_MAXW];
+    uint32_t nw[FB_MAX_NW], mw[FB_MAX_NW];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        const double *lb = ws_lb + p * N, *ub = ws_ub + p * N;
+        const uint32_t *cb = cand + p * NW, *sb = s_cand + p * NW, *db = deads + p * NW;
+        for (int k = 0; k < NW; ++k) nw[k] = 0;
+        for (int l = 0; l + 1 < net.L; ++l) {
+            const int out = net.dims[l + 1], bo = net.boff[l];
+            int nc = 0, nn = 0;
+            for (int j = 0; j < out; ++j) {
+                const int idx = bo + j;
+                if ((cb[idx >> 5] >> (idx & 31)) & 1u) cv[nc++] = ub[idx];
+                else nv[nn++] = ub[idx];
+            }
+            if (nn == 0) {
+                for (int j = 0; j < out; ++j) nw[(bo + j) >> 5] |= 1u << ((bo + j) & 31);
+                continue;
+            }
+            if (nc == 0) continue;
+            const double cmean = fb_np_mean(cv, nc), nmean = fb_np_mean(nv, nn);
+            fb_insertion_sort(cv, nc); fb_insertion_sort(nv, nn);
+            const double cmed = fb_np_median_sorted(cv, nc), nmed = fb_np_median_sorted(nv, nn);
+            const double n_lo = fb_np_percentile_sorted(nv, nn, pct);
+            const double n_hi = fb_np_percentile_sorted(nv, nn, __dadd_rn(100.0, -pct));
+            if (nmean > __dmul_rn(2.0, cmean) && nmed > __dmul_rn(2.0, cmed)) {
+                const double hi10 = __dmul_rn(0.1, n_hi);
+                for (int j = 0; j < out; ++j) {
+                    const int idx = bo + j;
+                    if (((sb[idx >> 5] >> (idx & 31)) & 1u) && ub[idx] < n_lo && ub[idx] < hi10 && ub[idx] < fabs(lb[idx]))
+                        nw[idx >> 5] |= 1u << (idx & 31);
+                }
+            }
+        }
+        for (int l = 0; l < net.L; ++l) fb_keep_one_bits(nw, net.boff[l], net.dims[l + 1]);
+        for (int k = 0; k < NW; ++k) mw[k] = db[k] | nw[k];
+        for (int l = 0; l < net.L; ++l) fb_keep_one_bits(mw, net.boff[l], net.dims[l + 1]);
+        for (int k = 0; k < NW; ++k) { new_deads[p * NW + k] = nw[k]; merged[p * NW + k] = mw[k]; }
+    }
+}
+
+extern "C" int fb_heuristic(const fb_model *m, int64_t n, const double *ws_lb, const double *ws_ub, const uint32_t *cand,
+                            const uint32_t *s_cand, const uint32_t *deads, double pct, uint32_t *new_deads,
+                            uint32_t *merged, void *stream)
+{
+    if (!m || n < 0) return fb_fail(FB_ERR_INVALID, "fb_heuristic: bad argument");
+    if (n == 0) return FB_OK;
+    if (!ws_lb || !ws_ub || !cand || !s_cand || !deads || !new_deads || !merged)
+        return fb_fail(FB_ERR_INVALID, "fb_heuristic: null argument");
+    if (!(pct >= 0.0 && pct <= 100.0)) return fb_fail(FB_ERR_INVALID, "fb_heuristic: percentile %g outside [0, 100]", pct);
+    const int grid = (int)std::min<int64_t>((n + 63) / 64, (int64_t)m->num_sms * 8);
+    fb_heuristic_kernel<<<grid, 64, 0, (cudaStream_t)stream>>>(m->gen, n, ws_lb, ws_ub, cand, s_cand, deads, pct, new_deads,
+                                                               merged);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // FP64 issue-rate microbenchmark: 8 independent DFMA chains per thread, enough warps to saturate the
 // pipe.  Gives the measured denominator for "% of FP64 peak".
 // ---------------------------------------------------------------------------------------------------

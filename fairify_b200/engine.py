@@ -257,6 +257,18 @@ class Model:
         check(fn(self._h, rows, _ptr(X), _ptr(dead), _ptr(out), _stream()), "fb_forward")
         return out
 
+    def heuristic(self, ws_lb, ws_ub, cand, s_cand, deads, pct):
+        """(new_deads, merged_deads) int32 mask tensors [n, NW]; inputs [n, N] float64 bounds and [n, NW] masks."""
+        ws_lb = self._dev(ws_lb, torch.float64).reshape(-1, self.N); ws_ub = self._dev(ws_ub, torch.float64).reshape(-1, self.N)
+        n = ws_lb.shape[0]
+        masks = [self._dev(np.asarray(x, dtype=np.uint32).view(np.int32) if not isinstance(x, torch.Tensor) else x,
+                           torch.int32).reshape(n, self.NW) for x in (cand, s_cand, deads)]
+        new = torch.empty((n, self.NW), dtype=torch.int32, device=self.device)
+        merged = torch.empty((n, self.NW), dtype=torch.int32, device=self.device)
+        check(_lib.lib().fb_heuristic(self._h, n, _ptr(ws_lb), _ptr(ws_ub), _ptr(masks[0]), _ptr(masks[1]), _ptr(masks[2]),
+                                      C.c_double(float(pct)), _ptr(new), _ptr(merged), _stream()), "fb_heuristic")
+        return new, merged
+
     def pair_screen(self, X, pa_cols, alts):
         """(orig_pred uint8 [m], first_flip int32 [m]) for float32 rows X and alternatives [k, n_pa]."""
         X = self._dev(X, torch.float32).reshape(-1, self.d); m = X.shape[0]

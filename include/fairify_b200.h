@@ -127,6 +127,14 @@ int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, cons
                         uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
                         int32_t *pa_neg, uint8_t *verdict, void *stream);
 
+/* -- heuristic_prune, utils/prune.py:862-939 (only reached after a Z3 `unknown`): per hidden layer compare the
+ *    ws_ub of sample-candidates and non-candidates (numpy mean / median / percentile semantics) and mark small-bound
+ *    candidates dead.  ws_lb, ws_ub [n][N]; cand = `candidates`, s_cand = `s_candidates`, deads = `deads`, all [n][NW];
+ *    pct = perc_threshold.  Outputs new_deads and merged_deads [n][NW], keep-one fix applied to both. */
+int fb_heuristic(const fb_model *m, int64_t n, const double *ws_lb, const double *ws_ub, const uint32_t *cand,
+                 const uint32_t *s_cand, const uint32_t *deads, double pct, uint32_t *new_deads, uint32_t *merged,
+                 void *stream);
+
 /* -- measurement aid: sustained DFMA issue rate of the current device, in TFLOP/s (FMA = 2 flops).
  *    This is the roofline denominator of the profile / interval kernels. */
 int fb_fp64_peak(int iters, double *tflops, double *ms);

@@ -48,6 +48,7 @@ def test_partition_grid_matches_reference(tag):
     random.shuffle(p_list)                                                     # the drivers shuffle the list
 
 
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ["GC-1", "GC-5", "AC-1", "AC-7", "BM-4", "BM-6"])
 def test_heuristic_prune_and_mask_helpers(name):
     from utils.prune import compression_ratio, dead_node_from_bound, heuristic_prune, merge_dead_nodes, prune_neurons

@@ -357,3 +357,20 @@ def test_two_rank_sharded_run_equals_single_rank(eng):
     mgr = mp.Manager(); ret = mgr.dict()
     mp.spawn(_two_rank_worker, args=(2, port, ret), nprocs=2, join=True)
     assert ret.get(0) and ret.get(1), dict(ret)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_heuristic_prune_batched(eng, name):
+    """fb_heuristic on all golden cases of a model at once, thresholds 5/20/50/100 (utils/prune.py:862-939)."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b)
+    cs = list(G.cases(name))
+    lb = np.stack([c["ws_lb"] for c in cs]); ub = np.stack([c["ws_ub"] for c in cs])
+    cand = eng.pack_bits(np.stack([c["cand"] for c in cs])); bc = eng.pack_bits(np.stack([c["b_cand"] for c in cs]))
+    bd = eng.pack_bits(np.stack([c["b_dead"] for c in cs]))
+    for pct in (5, 20, 50, 100):
+        new, merged = m.heuristic(lb, ub, cand, bc, bd, pct)
+        new = eng.unpack_bits(new.cpu().numpy().view(np.uint32), m.N); merged = eng.unpack_bits(merged.cpu().numpy().view(np.uint32), m.N)
+        for k, c in enumerate(cs):
+            assert np.array_equal(new[k], c[f"h{pct}_new"]), f"{c['tag']} pct={pct}"
+            assert np.array_equal(merged[k], c[f"h{pct}_merged"]), f"{c['tag']} pct={pct}"

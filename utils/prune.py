@@ -16,8 +16,9 @@ What runs where
     box (it is ws_ub), so the query is only run for neurons whose bound is within rounding error of zero
     ("slivers").  FAIRIFY_GPU_SINGULAR=reference runs it for every remaining candidate like the reference,
     =off never runs it.  s_dead is all-zero in every published result and every fixture.
-  * `prune_neurons`, `compression_ratio`, `merge_dead_nodes`, `heuristic_prune` operate on a handful of
-    Python lists per partition and feed Z3; they stay host code.
+  * `heuristic_prune` (:862-939) runs on the device too (`fb_heuristic`);
+  * `prune_neurons`, `compression_ratio`, `merge_dead_nodes` operate on a handful of Python lists per
+    partition and feed Z3; they stay host code.
 """
 import copy
 import os
@@ -268,25 +269,13 @@ def harsh_prune(df, weight, bias, simulation_size, layer_net, range_dict):
 # heuristic_prune (reference :862-939): only reached after a Z3 `unknown`; a few numpy statistics per layer
 # ----------------------------------------------------------------------------------------------------
 def heuristic_prune(bounds, candidates, s_candidates, deads, pos_prob, perc_threshold, w, b):
+    """(new_deads, merged_deads), computed on the device (`fb_heuristic`) from the reference's list arguments."""
+    from fairify_b200.engine import pack_bits, unpack_bits
     ws_lb, ws_ub, pl_lb, pl_ub = bounds
-    new_deads = [[0] * len(l) for l in candidates]
-    for l in range(len(candidates) - 1):
-        cand = [ws_ub[l][j] for j in range(len(candidates[l])) if candidates[l][j]]
-        noncand = [ws_ub[l][j] for j in range(len(candidates[l])) if not candidates[l][j]]
-        if len(noncand) == 0:
-            for j in range(len(s_candidates[l])):
-                new_deads[l][j] = 1
-            continue
-        if len(cand) == 0:
-            continue
-        c, n = np.array(cand), np.array(noncand)
-        if np.mean(n) > 2 * np.mean(c) and np.median(n) > 2 * np.median(c):
-            low = np.percentile(n, perc_threshold)
-            high = np.percentile(n, 100 - perc_threshold)
-            for j in range(len(s_candidates[l])):
-                if s_candidates[l][j] and ws_ub[l][j] < low and ws_ub[l][j] < 0.1 * high \
-                        and ws_ub[l][j] < abs(ws_lb[l][j]):
-                    new_deads[l][j] = 1
-    _keep_one(new_deads)
-    merged = _keep_one(merge_dead_nodes(deads, new_deads))
-    return new_deads, merged
+    m = _device.model_for(w, b)
+    flat = lambda ll: np.concatenate([np.asarray(l, dtype=np.float64) for l in ll])[None]
+    bits = lambda ll: pack_bits(np.concatenate([np.asarray(l, dtype=np.uint8) != 0 for l in ll]).astype(np.uint8)[None])
+    new, merged = m.heuristic(flat(ws_lb), flat(ws_ub), bits(candidates), bits(s_candidates), bits(deads), perc_threshold)
+    new = unpack_bits(new.cpu().numpy().view(np.uint32), m.N)[0]
+    merged = unpack_bits(merged.cpu().numpy().view(np.uint32), m.N)[0]
+    return _split_lists(m, new, int), _split_lists(m, merged, int)
