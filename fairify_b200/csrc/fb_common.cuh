@@ -30,8 +30,13 @@ __device__ __forceinline__ void fb_philox4x32_10(uint32_t c0, uint32_t c1, uint3
     for (int r = 0; r < 10; ++r) {
         // (written with separate high/low products: measured faster on sm_100a than the 64-bit-product form,
         //  which costs extra register moves in the fully unrolled profile kernel)
+#if defined(FB_PHILOX_WIDE) && FB_PHILOX_WIDE
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0, hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+#else
         const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
         const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+#endif
         const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
         c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;

@@ -12,22 +12,63 @@
 // Visit::neuron(idx, last, pre) returns the activation fed to the next layer; idx and last fold to
 // constants because every call site is inside fully unrolled loops.
 // ---------------------------------------------------------------------------------------------------
+//
+// Layers are evaluated in pairs so that a wide hidden layer never sits in registers: layer l goes neuron by
+// neuron (terms i ascending), and each finished activation h_j is folded at once into the accumulators of
+// layer l+1 (acc2[k] += w2[j][k] * h_j), whose own terms thereby also arrive for j ascending.  Every neuron
+// of either layer still sees one fused multiply-add per term in ascending input order and its bias last, so
+// the results are bit-identical to the plain layer-by-layer evaluation (and to the oracle).  Live state is the
+// inputs of layer l plus the accumulators of layer l+1 -- e.g. 13 + 1 values for a 13-100-1 network instead
+// of 13 + 100.
+#ifndef FB_SPEC_JB
+#define FB_SPEC_JB 1            // neurons of layer l evaluated together (1 measured best; 2-8 need more registers than they save)
+#endif
 template <class S, int l, typename T, class PRM, class Visit>
 __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
 {
-    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
-    constexpr bool last = (l == S::NL - 1);
-    T y[OUT];
+    constexpr int IN = S::dim(l), M = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
+    constexpr bool has_next = (l + 1 < S::NL);
+    constexpr int L2 = has_next ? l + 1 : l;                      // (kept in range when there is no next layer)
+    constexpr int M2 = has_next ? S::dim(L2 + 1) : 1, WO2 = S::woff(L2), BO2 = S::boff(L2);
+    T acc2[M2];
 #pragma unroll
-    for (int j = 0; j < OUT; ++j) {
-        T acc = T(0.0);
+    for (int k = 0; k < M2; ++k) acc2[k] = T(0.0);
+    T h = T(0.0);
+    // neurons of layer l in blocks of FB_SPEC_JB: inside a block the inputs are walked once and each x_i feeds
+    // JB independent accumulators whose weights w[i][j0 .. j0+JB) are adjacent in the constant bank (one wide
+    // uniform load per pair), which gives the FP64 pipe JB * K independent chains instead of K
 #pragma unroll
-        for (int i = 0; i < IN; ++i) acc = fb_fma(prm.w[WO + i * OUT + j], x[i], acc);
-        const T pre = fb_add(acc, prm.b[BO + j]);
-        y[j] = v.neuron(BO + j, last, pre);
+    for (int j0 = 0; j0 < M; j0 += FB_SPEC_JB) {
+        constexpr int JBmax = FB_SPEC_JB;
+        T acc[JBmax];
+#pragma unroll
+        for (int jj = 0; jj < JBmax; ++jj) acc[jj] = T(0.0);
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+#pragma unroll
+            for (int jj = 0; jj < JBmax; ++jj)
+                if (j0 + jj < M) acc[jj] = fb_fma(prm.w[WO + i * M + j0 + jj], x[i], acc[jj]);
+        }
+#pragma unroll
+        for (int jj = 0; jj < JBmax; ++jj) {
+            if (j0 + jj < M) {
+                h = v.neuron(BO + j0 + jj, !has_next, fb_add(acc[jj], prm.b[BO + j0 + jj]));
+                if constexpr (has_next) {
+#pragma unroll
+                    for (int k = 0; k < M2; ++k) acc2[k] = fb_fma(prm.w[WO2 + (j0 + jj) * M2 + k], h, acc2[k]);
+                }
+            }
+        }
     }
-    if constexpr (last) return y[0];
-    else return fb_spec_forward<S, l + 1, T, PRM, Visit>(prm, y, v);
+    if constexpr (!has_next) return h;                            // the network's single logit (M == 1)
+    else {
+        constexpr bool last2 = (l + 2 == S::NL);
+        T y2[M2];
+#pragma unroll
+        for (int k = 0; k < M2; ++k) y2[k] = v.neuron(BO2 + k, last2, fb_add(acc2[k], prm.b[BO2 + k]));
+        if constexpr (last2) return y2[0];
+        else return fb_spec_forward<S, l + 2, T, PRM, Visit>(prm, y2, v);
+    }
 }
 
 // plain ReLU visitor (logit only)
@@ -69,11 +110,59 @@ struct FbMaskedVisit {
 #ifndef FB_PROFILE_MINB
 #define FB_PROFILE_MINB 4                                // minimum resident CTAs per SM (caps registers at 128)
 #endif
-#define FB_PROFILE_MAX_STEPS (255 / FB_PROFILE_SPT)      // per-lane counters are 8-bit fields
+#define FB_PROFILE_MAX_STEPS (127 / FB_PROFILE_SPT)      // per-lane counters hold up to 127 (7 bit planes)
 
 // per-lane packed 8-bit counters, one field per neuron
+#ifndef FB_PROFILE_BITSLICE
+#define FB_PROFILE_BITSLICE 1        // 1: per-sample non-zero bit masks + bit-sliced counters, 0: packed 8-bit counters
+#endif
+#define FB_PROFILE_PLANES 7          // bit-sliced counters count to 127 per lane
+
 template <int N, int K>
 struct FbCountVisit {
+#if FB_PROFILE_BITSLICE
+    // One bit per neuron and sample: neuron idx sets bit idx of nzmask[k].  After the forward pass the masks
+    // are added into `planes`, a bit-sliced counter (planes[b] holds bit b of every neuron's count): two
+    // logic ops per plane add one sample to ALL neurons' counters at once, and the activity flag of a ragged
+    // step is applied to the whole mask in one AND instead of once per neuron.
+    static constexpr int NW = (N + 31) / 32;
+    uint32_t nzmask[K][NW];
+    __device__ __forceinline__ void begin()
+    {
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int w = 0; w < NW; ++w) nzmask[k][w] = 0;
+    }
+    __device__ __forceinline__ VecD<K> neuron(int idx, bool last, const VecD<K> &pre)
+    {
+        VecD<K> r;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const bool pos = fb_pos(pre.v[k]);
+            const bool nz = last ? fb_nonzero(pre.v[k]) : pos;
+            if (nz) nzmask[k][idx >> 5] |= 1u << (idx & 31);
+            r.v[k] = last ? pre.v[k] : (pos ? pre.v[k] : 0.0);
+        }
+        return r;
+    }
+    // planes += nzmask[k] (restricted to active samples)
+    __device__ __forceinline__ void commit(uint32_t (&planes)[FB_PROFILE_PLANES][NW], const bool (&active)[K])
+    {
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                uint32_t carry = active[k] ? nzmask[k][w] : 0u;
+#pragma unroll
+                for (int b = 0; b < FB_PROFILE_PLANES; ++b) {
+                    const uint32_t t = planes[b][w] & carry;
+                    planes[b][w] ^= carry;
+                    carry = t;
+                }
+            }
+    }
+#else
     uint32_t (&cnt)[(N + 3) / 4];
     bool active[K];             // false for sample slots past the end of the chunk (ragged last step)
     __device__ __forceinline__ VecD<K> neuron(int idx, bool last, const VecD<K> &pre)
@@ -88,6 +177,7 @@ struct FbCountVisit {
         }
         return r;
     }
+#endif
 };
 
 template <class S, int l, typename T, class PRM, class Visit>
@@ -222,10 +312,28 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
                 lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
             }
         }
+        const int64_t pidx = first_index + p;
+#if FB_PROFILE_BITSLICE
+        constexpr int NWm = (N + 31) / 32;
+        uint32_t planes[FB_PROFILE_PLANES][NWm];
+#pragma unroll
+        for (int b = 0; b < FB_PROFILE_PLANES; ++b)
+#pragma unroll
+            for (int w = 0; w < NWm; ++w) planes[b][w] = 0;
+        for (int sb = s0; sb < s1; sb += 32 * K) {
+            FbCountVisit<N, K> vis;
+            vis.begin();
+            bool active[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) active[k] = (sb + 32 * k + lane) < s1;
+            fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
+                                          s1 - 1);
+            vis.commit(planes, active);
+        }
+#else
         uint32_t cnt[(N + 3) / 4];
 #pragma unroll
         for (int k = 0; k < (N + 3) / 4; ++k) cnt[k] = 0;
-        const int64_t pidx = first_index + p;
         // one copy of the unrolled network: the ragged last step is handled by the per-sample activity flags
         // (a second, flag-free copy for the full steps doubles the code and loses more in instruction fetch
         // than the flags cost)
@@ -236,10 +344,18 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
             fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
                                           s1 - 1);
         }
+#endif
         uint32_t mine = 0;
 #pragma unroll
         for (int j = 0; j < N; ++j) {
+#if FB_PROFILE_BITSLICE
+            uint32_t mycount = 0;
+#pragma unroll
+            for (int b = 0; b < FB_PROFILE_PLANES; ++b) mycount |= ((planes[b][j >> 5] >> (j & 31)) & 1u) << b;
+            const uint32_t tot = __reduce_add_sync(0xffffffffu, mycount);
+#else
             const uint32_t tot = __reduce_add_sync(0xffffffffu, (cnt[j >> 2] >> (8 * (j & 3))) & 0xffu);
+#endif
             if ((j & 31) == lane) mine = tot;
             if ((j & 31) == 31 || j == N - 1) {
                 const int jj = (j & ~31) + lane;
