@@ -301,7 +301,9 @@ def run_gpu(args):
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("profile_kernel_dram_bytes_per_launch")
+            # measured DRAM bytes per partition (ncu --set full, profiles/r1_profile_kernel_ncu.csv) x this launch's size
+            per_part = json.load(open(tpath)).get("profile_kernel_dram_bytes_per_partition")
+            traffic = None if per_part is None else per_part * n
         except Exception:
             traffic = None
     peaks = {}
