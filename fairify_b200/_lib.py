@@ -14,7 +14,7 @@ SO_PATH = os.environ.get("FAIRIFY_B200_LIB") or os.path.join(_HERE, "libfairify_
 # every symbol include/fairify_b200.h declares
 EXPORTS = [
     "fb_version", "fb_last_error", "fb_num_sms", "fb_model_create", "fb_model_destroy", "fb_model_info",
-    "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_profile", "fb_ibp", "fb_prune",
+    "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_grid_locate", "fb_profile", "fb_ibp", "fb_prune",
     "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_heuristic", "fb_fp64_peak",
 ]
 
@@ -52,6 +52,7 @@ def lib():
     L.fb_grid_destroy.argtypes = [vp]; L.fb_grid_destroy.restype = None
     L.fb_grid_size.argtypes = [vp]; L.fb_grid_size.restype = i64
     L.fb_grid_boxes.argtypes = [vp, i64, i64, vp, vp]
+    L.fb_grid_locate.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_profile.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, vp]
     L.fb_ibp.argtypes = [vp, i64, vp, vp, vp, C.POINTER(PruneOut), vp]
     L.fb_prune.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, C.POINTER(PruneOut), vp]

@@ -260,6 +260,47 @@ extern "C" int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int
     return FB_OK;
 }
 
+// point -> partition index (and per-partition row counts): the membership test of
+// find_partition_result_for_point (src/AC/Verify-AC-experiment-new2.py:587-611) and p_list_density
+// (utils/input_partition.py:184-218) as O(d) index arithmetic per row instead of a scan over all partitions
+__global__ void __launch_bounds__(256)
+fb_grid_locate_kernel(const FbGridDesc g, int64_t m, const double *__restrict__ X, int64_t *__restrict__ index,
+                      unsigned int *__restrict__ density)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+        int64_t idx = 0;
+        bool ok = true;
+        for (int k = 0; k < g.d && ok; ++k) {
+            const int c = g.col[k];
+            const double x = X[r * g.d + c];
+            if (!(x >= (double)g.lo[c] && x <= (double)g.hi[c])) { ok = false; break; }
+            int64_t digit = 0;
+            if (g.nch[c] > 1) {
+                digit = (int64_t)floor(__ddiv_rn(__dadd_rn(x, -(double)g.lo[c]), (double)g.T));
+                const int64_t top = min(g.lo[c] + digit * g.T + g.T - 1, g.hi[c]);
+                if (x > (double)top) { ok = false; break; }
+            }
+            idx = idx * g.nch[c] + digit;
+        }
+        if (index) index[r] = ok ? idx : -1;
+        if (density && ok) atomicAdd(&density[idx], 1u);
+    }
+}
+
+extern "C" int fb_grid_locate(const fb_grid *g, int64_t m, const double *X, int64_t *index, uint32_t *density, void *stream)
+{
+    if (!g || m < 0) return fb_fail(FB_ERR_INVALID, "fb_grid_locate: bad argument");
+    if (m == 0) return FB_OK;
+    if (!X || (!index && !density)) return fb_fail(FB_ERR_INVALID, "fb_grid_locate: null argument");
+    int sms = 0;
+    if (fb_num_sms(&sms)) return FB_ERR_CUDA;
+    const int grid = (int)std::min<int64_t>((m + 255) / 256, (int64_t)sms * 8);
+    fb_grid_locate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g->g, m, X, index, density);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // profile
 // ---------------------------------------------------------------------------------------------------

@@ -336,6 +336,20 @@ class Grid:
         return out
 
 
+def _grid_locate(self, X, want_index=True, want_density=False):
+    """(index int64 [m] or None, density int32 [size] or None) for rows X [m, d] (column order)."""
+    X = torch.as_tensor(np.ascontiguousarray(X, dtype=np.float64)).to(self.device) if not isinstance(X, torch.Tensor) \
+        else X.to(device=self.device, dtype=torch.float64).contiguous()
+    m = X.shape[0]
+    index = torch.empty((m,), dtype=torch.int64, device=self.device) if want_index else None
+    density = torch.zeros((self.size,), dtype=torch.int32, device=self.device) if want_density else None
+    check(_lib.lib().fb_grid_locate(self._h, m, _ptr(X), _ptr(index), _ptr(density), _stream()), "fb_grid_locate")
+    return index, density
+
+
+Grid.locate = _grid_locate
+
+
 def fp64_peak(iters=4096):
     """Measured DFMA rate of the current device in TFLOP/s (FMA = 2 flops) and the kernel time in ms."""
     _require_cuda()

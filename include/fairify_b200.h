@@ -75,6 +75,12 @@ int64_t fb_grid_size(const fb_grid *g);
 /* boxes [count][d][2] for canonical (itertools.product) indices first .. first+count-1 */
 int fb_grid_boxes(const fb_grid *g, int64_t first, int64_t count, int32_t *boxes, void *stream);
 
+/* point -> partition: canonical index of the box containing each row of X (float64 [m][d], column order), -1 if none;
+ * replaces the linear scans of find_partition_result_for_point (src/AC/Verify-AC-experiment-new2.py:587-611) and
+ * p_list_density (utils/input_partition.py:184-218).  index int64 [m] and/or density uint32 [grid size] (rows per
+ * partition, ADDED to what is there: zero it first); either may be NULL. */
+int fb_grid_locate(const fb_grid *g, int64_t m, const double *X, int64_t *index, uint32_t *density, void *stream);
+
 /* -- activation profile: candidate_dead_nodes, utils/prune.py:168-192 (+ simluate_data :205-222) -- */
 /* counts uint32 [n][N].  first_index = global index of boxes[0] (Philox counter; keeps shards identical) */
 int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,

@@ -114,6 +114,34 @@ void fo_grid_boxes(int d, const int64_t *lo, const int64_t *hi, int64_t T, const
     }
 }
 
+/* Point -> partition: canonical index of the box containing each row of X (float64 [m][d], column order),
+ * or -1 when no box does (outside the domain, or between two integer chunks).  Restates the membership test
+ * of find_partition_result_for_point (src/AC/Verify-AC-experiment-new2.py:587-611: lower <= x <= upper for
+ * every attribute) and of p_list_density (utils/input_partition.py:198-212), with the linear scan over all
+ * partitions replaced by the mixed-radix index arithmetic of the grid. */
+void fo_grid_locate(int d, const int64_t *lo, const int64_t *hi, int64_t T, const int32_t *key_order, int64_t m,
+                    const double *X, int64_t *index)
+{
+    int64_t nch[64];
+    fo_grid_count(d, lo, hi, T, nch);
+    for (int64_t r = 0; r < m; ++r) {
+        int64_t idx = 0; int ok = 1;
+        for (int k = 0; k < d && ok; ++k) {               /* first key is the slowest digit */
+            int c = key_order[k];
+            double x = X[r * d + c];
+            if (!(x >= (double)lo[c] && x <= (double)hi[c])) { ok = 0; break; }
+            int64_t digit = 0;
+            if (nch[c] > 1) {
+                digit = (int64_t)floor((x - (double)lo[c]) / (double)T);
+                int64_t top = lo[c] + digit * T + T - 1; if (top > hi[c]) top = hi[c];
+                if (x > (double)top) { ok = 0; break; }
+            }
+            idx = idx * nch[c] + digit;
+        }
+        index[r] = ok ? idx : -1;
+    }
+}
+
 /* ------------------------------------------------------------------------------------------------
  * a6: neuron_bounds, utils/prune.py:105-164, float64 semantics of the reference's pinned numpy
  * (weights cast to float64 first).  Per neuron: min_t = max_t = 0; for i ascending the product is

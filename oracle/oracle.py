@@ -75,6 +75,15 @@ def grid_boxes(lo, hi, T, key_order, first, count):
     return out
 
 
+def grid_locate(lo, hi, T, key_order, X):
+    lo = np.ascontiguousarray(lo, dtype=np.int64); hi = np.ascontiguousarray(hi, dtype=np.int64)
+    ko = np.ascontiguousarray(key_order, dtype=np.int32)
+    X = np.ascontiguousarray(X, dtype=np.float64); m = X.shape[0]
+    out = np.zeros(m, dtype=np.int64)
+    lib().fo_grid_locate(len(lo), _p(lo), _p(hi), C.c_int64(T), _p(ko), C.c_int64(m), _p(X), _p(out))
+    return out
+
+
 def ibp(net, boxes):
     boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
     outs = [np.zeros((n, net.N)) for _ in range(4)]

@@ -55,6 +55,13 @@ def load():
         aif.datasets = ds
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
+    if "utils" not in sys.modules:
+        # the reference's utils/ has no __init__.py (a namespace package), so this repo's regular `utils` package
+        # would win the path scan wherever it sits on sys.path: bind the name to the reference directory explicitly
+        pkg = types.ModuleType("utils")
+        pkg.__path__ = [os.path.join(REFERENCE_ROOT, "utils")]
+        pkg.__file__ = os.path.join(REFERENCE_ROOT, "utils", "__init__.py")
+        sys.modules["utils"] = pkg
     with contextlib.redirect_stdout(io.StringIO()):
         prune = importlib.import_module("utils.prune")
         part = importlib.import_module("utils.input_partition")

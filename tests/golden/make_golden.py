@@ -275,6 +275,29 @@ def main():
     np_stats()
     prune_cases(ref, weights)
     causal_cases(weights)
+    density_case(ref)
+
+
+
+def density_case(ref):
+    """p_list_density (utils/input_partition.py:184-218) on a synthetic Adult frame: rows per partition / rows."""
+    D = domains.DOMAINS["AC"]
+    rng = np.random.RandomState(11)
+    out = {}
+    for tag, T, nrows in (("AC_T30", 30, 400), ("AC_T12", 12, 250)):
+        rd = D.copy_ranges()
+        p_dict = ref.input_partition.partition(rd, T)
+        p_list = ref.input_partition.partitioned_ranges(rd.keys(), D.pa, p_dict, rd)
+        lo = np.array([rd[c][0] for c in D.columns]); hi = np.array([rd[c][1] for c in D.columns])
+        X = rng.randint(lo, hi + 1, size=(nrows, D.d))
+        X[::17, 0] = 5                      # a few rows below the age range: they fall in no partition
+        X[5::23, 11] = 150                  # and above the hours-per-week range
+        df = pd.DataFrame(np.column_stack([X, rng.randint(0, 2, size=nrows)]), columns=D.columns + [D.label])
+        dens = ref.input_partition.p_list_density(D.copy_ranges(), p_list, df)     # (the reference overwrites its range_dict argument)
+        out[f"{tag}/T"] = np.int64(T); out[f"{tag}/X"] = X.astype(np.int64); out[f"{tag}/density"] = np.array(dens)
+        out[f"{tag}/n"] = np.int64(len(p_list))
+        print(f"density {tag}: {len(p_list)} partitions, {nrows} rows, covered {sum(dens):.3f}")
+    np.savez_compressed(os.path.join(HERE, "density.npz"), **out)
 
 
 if __name__ == "__main__":

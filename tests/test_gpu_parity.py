@@ -374,3 +374,23 @@ def test_heuristic_prune_batched(eng, name):
         for k, c in enumerate(cs):
             assert np.array_equal(new[k], c[f"h{pct}_new"]), f"{c['tag']} pct={pct}"
             assert np.array_equal(merged[k], c[f"h{pct}_merged"]), f"{c['tag']} pct={pct}"
+
+
+@pytest.mark.parametrize("tag", ["AC_T30", "AC_T12"])
+def test_grid_locate_and_density(eng, tag):
+    """fb_grid_locate == oracle == the reference's p_list_density; the drop-in p_list_density goes through it."""
+    import pandas as pd
+    from fairify_b200.domains import DOMAINS
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "density.npz"))
+    D = DOMAINS["AC"]; T = int(z[f"{tag}/T"]); X = z[f"{tag}/X"]
+    grid = eng.Grid(D.columns, D.ranges, T)
+    idx, dens = grid.locate(X.astype(np.float64), want_density=True)
+    lo = [D.ranges[c][0] for c in D.columns]; hi = [D.ranges[c][1] for c in D.columns]
+    ko = [D.columns.index(k) for k in D.ranges.keys()]
+    assert np.array_equal(idx.cpu().numpy(), O.grid_locate(lo, hi, T, ko, X))
+    assert np.array_equal(dens.cpu().numpy() / X.shape[0], z[f"{tag}/density"])
+    from utils.input_partition import p_list_density, partition, partitioned_ranges
+    rd = D.copy_ranges()
+    p_list = partitioned_ranges(rd.keys(), D.pa, partition(rd, T), rd)
+    df = pd.DataFrame(np.column_stack([X, np.zeros(len(X), dtype=np.int64)]), columns=D.columns + [D.label])
+    assert p_list_density(D.copy_ranges(), p_list, df) == list(z[f"{tag}/density"])

@@ -1,6 +1,7 @@
 """CPU: the oracle (oracle/fairify_oracle.c) against the golden vectors the UNMODIFIED reference produced
 (tests/golden/make_golden.py).  This is what pins the oracle; the GPU tests then compare against it."""
 import hashlib
+import os
 
 import numpy as np
 import pytest
@@ -141,3 +142,26 @@ def test_philox_samples_in_range_and_uniform():
         vals, cnt = np.unique(s[:, i], return_counts=True)
         assert len(vals) == boxes[0, i, 1] - boxes[0, i, 0] + 1
         assert cnt.min() > 0.7 * 4000 / len(vals)
+
+
+@pytest.mark.parametrize("tag", ["AC_T30", "AC_T12"])
+def test_point_to_partition_density(tag):
+    """p_list_density (utils/input_partition.py:184-218): rows per partition via index arithmetic == the reference's scan."""
+    from fairify_b200.domains import DOMAINS
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "density.npz"))
+    D = DOMAINS["AC"]
+    lo = [D.ranges[c][0] for c in D.columns]; hi = [D.ranges[c][1] for c in D.columns]
+    ko = [D.columns.index(k) for k in D.ranges.keys()]
+    X = z[f"{tag}/X"]; n = int(z[f"{tag}/n"])
+    idx = O.grid_locate(lo, hi, int(z[f"{tag}/T"]), ko, X)
+    dens = np.bincount(idx[idx >= 0], minlength=n) / X.shape[0]
+    assert np.array_equal(dens, z[f"{tag}/density"])
+    # located boxes really contain their rows
+    boxes = O.grid_boxes(lo, hi, int(z[f"{tag}/T"]), ko, 0, n)
+    inside = idx >= 0
+    b = boxes[idx[inside]]
+    assert np.all((X[inside] >= b[:, :, 0]) & (X[inside] <= b[:, :, 1]))
+    assert not np.any(np.all((X[~inside][:, None, :] >= boxes[None, :, :, 0]) & (X[~inside][:, None, :] <= boxes[None, :, :, 1]), axis=2))
+    # non-integer points between two chunks belong to no partition
+    Xf = X[inside][:5].astype(np.float64); Xf[:, 0] = 39.5 if int(z[f"{tag}/T"]) == 30 else 21.5
+    assert np.all(O.grid_locate(lo, hi, int(z[f"{tag}/T"]), ko, Xf) == -1)

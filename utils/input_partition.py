@@ -118,9 +118,20 @@ def partitioned_ranges_df(A, PA, p_dict, range_dict, max_partitions=100):
 
 
 def p_list_density(range_dict, p_list, df):
-    """Fraction of dataset rows falling in each partition (reference :184-218), vectorised on the host."""
+    """Fraction of dataset rows falling in each partition (reference :184-218).  For a list that came from
+    `partitioned_ranges` the rows are located on the device by index arithmetic (`fb_grid_locate`); any other list
+    of boxes is compared on the host."""
     data = df.drop(labels=['income-per-year'], axis=1, inplace=False)
     total = df.shape[0]
+    if isinstance(p_list, PartitionList) and p_list.uniform_threshold() is not None and len(p_list) > 0 \
+            and all(isinstance(p, PartitionBox) for p in p_list):
+        from fairify_b200 import engine
+        cols = list(data.columns)
+        grid = engine.Grid(cols, p_list.range_dict, p_list.uniform_threshold())
+        if len(grid) == len(p_list):
+            _, dens = grid.locate(data[cols].to_numpy().astype(np.float64), want_index=False, want_density=True)
+            dens = dens.cpu().numpy()
+            return [int(dens[p.index]) / total for p in p_list]
     cols = list(range_dict.keys())
     X = data[cols].to_numpy()
     out = []
