@@ -104,6 +104,9 @@ struct FbMaskedVisit {
 #ifndef FB_PROFILE_SPT
 #define FB_PROFILE_SPT 2                                 // samples per lane per step
 #endif
+#ifndef FB_PROFILE_SPT_LIVE_MAX
+#define FB_PROFILE_SPT_LIVE_MAX 26                       // inputs + next-layer accumulators per sample that still fit
+#endif
 #ifndef FB_PROFILE_IM
 #define FB_PROFILE_IM 0                                  // 1: input-major forward, 0: output-major (measured best)
 #endif
@@ -285,6 +288,19 @@ __device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm
     }
 }
 
+// Samples per lane for shape S: FB_PROFILE_SPT (2) when the live state of the widest layer pair -- the inputs of
+// layer l plus the accumulators of layer l+1, per sample -- fits the 128-register budget, else 1.
+template <class S>
+__host__ __device__ constexpr int fb_profile_spt()
+{
+    int worst = 0;
+    for (int l = 0; l < S::NL; l += 2) {
+        const int live = S::dim(l) + (l + 2 <= S::NL ? S::dim(l + 2) : 1);
+        if (live > worst) worst = live;
+    }
+    return worst <= FB_PROFILE_SPT_LIVE_MAX ? FB_PROFILE_SPT : 1;
+}
+
 // counts[p][N] (uint32): stored when chunks == 1, atomically added otherwise (caller zeroes first).
 template <class S, bool PHILOX>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS, FB_PROFILE_MINB)
@@ -292,7 +308,7 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
                        const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
                        int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *__restrict__ counts)
 {
-    constexpr int D0 = S::D0, N = S::N, K = FB_PROFILE_SPT;
+    constexpr int D0 = S::D0, N = S::N, K = fb_profile_spt<S>();
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
