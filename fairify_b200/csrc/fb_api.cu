@@ -69,7 +69,7 @@ struct fb_model {
 static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
 {
     const FbSpecTable *tables[] = {&fb_spec_table_a, &fb_spec_table_b, &fb_spec_table_c, &fb_spec_table_d,
-                                   &fb_spec_table_e};
+                                   &fb_spec_table_e, &fb_spec_table_f};
     for (const FbSpecTable *t : tables)
         for (int k = 0; k < t->count; ++k) {
             const FbSpecEntry &e = t->entries[k];

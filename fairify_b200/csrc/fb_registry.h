@@ -40,4 +40,4 @@ struct FbSpecTable {
 };
 
 // defined in fb_spec_*.cu
-extern const FbSpecTable fb_spec_table_a, fb_spec_table_b, fb_spec_table_c, fb_spec_table_d, fb_spec_table_e;
+extern const FbSpecTable fb_spec_table_a, fb_spec_table_b, fb_spec_table_c, fb_spec_table_d, fb_spec_table_e, fb_spec_table_f;
