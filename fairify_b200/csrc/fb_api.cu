@@ -177,6 +177,21 @@ extern "C" int fb_model_info(const fb_model *m, int *L, int *N, int *P, int *spe
     return FB_OK;
 }
 
+// Scratch and staging buffers come from the device's stream-ordered pool.  By default that pool hands memory back
+// to the driver at every synchronisation, so a caller looping over fb_prune_host would re-acquire gigabytes per
+// call; keep freed blocks cached in the pool instead (once per device).
+static void fb_pool_keep_cached(int device)
+{
+    static bool done[64] = {};
+    if (device < 0 || device >= 64 || done[device]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    done[device] = true;
+}
+
 // set FAIRIFY_B200_FORCE_GENERIC=1 to route every model through the runtime-shape kernels (tests)
 static bool fb_use_spec(const fb_model *m)
 {
@@ -453,6 +468,7 @@ extern "C" int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, cons
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     uint32_t *counts = nullptr;
+    fb_pool_keep_cached(m->device);
     FB_CUDA(cudaMallocAsync(&counts, sizeof(uint32_t) * n * m->gen.N, st));
     int rc = fb_profile(m, n, boxes, samples, S, seed, first_index, counts, stream);
     if (rc == FB_OK) rc = fb_ibp(m, n, boxes, counts, tol, out, stream);
@@ -479,6 +495,7 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const int N = m->gen.N, NW = (N + 31) / 32, d = m->gen.dims[0];
+    fb_pool_keep_cached(m->device);
     DevBuf dboxes(st), dsamp(st), dtol(st);
     FB_CUDA(dboxes.alloc(sizeof(int32_t) * n * d * 2));
     FB_CUDA(cudaMemcpyAsync(dboxes.p, boxes, sizeof(int32_t) * n * d * 2, cudaMemcpyHostToDevice, st));
@@ -605,6 +622,7 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
     cudaStream_t st = (cudaStream_t)stream;
     int chunks, chunk_len;
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
+    fb_pool_keep_cached(m->device);
     DevBuf key(st);
     FB_CUDA(key.alloc(sizeof(unsigned long long) * n));
     FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));

@@ -100,18 +100,24 @@ struct FbMaskedVisit {
 // uniform constant-bank fetch of a weight feed K fused multiply-adds, and lets layer 0 take each feature
 // from a generator right where it is consumed (a sample's 13..30 features never sit in registers together).
 // ---------------------------------------------------------------------------------------------------
-#define FB_PROFILE_THREADS 128
+#ifndef FB_PROFILE_THREADS
+#define FB_PROFILE_THREADS 256
+#endif
 #ifndef FB_PROFILE_SPT
 #define FB_PROFILE_SPT 2                                 // samples per lane per step
 #endif
 #ifndef FB_PROFILE_SPT_LIVE_MAX
 #define FB_PROFILE_SPT_LIVE_MAX 26                       // inputs + next-layer accumulators per sample that still fit
 #endif
+#ifndef FB_PROFILE_SMEM_BOX
+#define FB_PROFILE_SMEM_BOX 1
+#endif
+#define FB_BOX_QUAL const
 #ifndef FB_PROFILE_IM
 #define FB_PROFILE_IM 0                                  // 1: input-major forward, 0: output-major (measured best)
 #endif
 #ifndef FB_PROFILE_MINB
-#define FB_PROFILE_MINB 4                                // minimum resident CTAs per SM (caps registers at 128)
+#define FB_PROFILE_MINB 2                                // minimum resident CTAs per SM (caps registers at 128)
 #endif
 #define FB_PROFILE_MAX_STEPS (127 / FB_PROFILE_SPT)      // per-lane counters hold up to 127 (7 bit planes)
 
@@ -230,8 +236,8 @@ __device__ __forceinline__ T fb_spec_forward_gen_in(const PRM &prm, XGen &xg, Vi
 // layer-0 input generators: feature(i) is called for i = 0, 1, ... in order
 template <int D0, int K>
 struct FbPhiloxGen {
-    const int32_t (&lo)[D0];
-    const uint32_t (&range)[D0];
+    FB_BOX_QUAL int32_t (&lo)[D0];
+    FB_BOX_QUAL uint32_t (&range)[D0];
     int s;                      // this lane's first sample of the step; its k-th sample is s + 32*k
     int64_t pidx;
     uint64_t seed;
@@ -265,8 +271,8 @@ struct FbInjectGen {
 
 // one step of the profile: this lane's K samples (indices s, s+32, ...) through the whole network
 template <class S, int K, bool PHILOX, class Visit>
-__device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm, Visit &vis, const int32_t (&lo)[S::D0],
-                                                const uint32_t (&range)[S::D0], const int32_t *part_samples, int s,
+__device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm, Visit &vis, FB_BOX_QUAL int32_t (&lo)[S::D0],
+                                                FB_BOX_QUAL uint32_t (&range)[S::D0], const int32_t *part_samples, int s,
                                                 int64_t pidx, uint64_t seed, int s_clamp = 0x7fffffff)
 {
     constexpr int D0 = S::D0;
@@ -301,6 +307,14 @@ __host__ __device__ constexpr int fb_profile_spt()
     return worst <= FB_PROFILE_SPT_LIVE_MAX ? FB_PROFILE_SPT : 1;
 }
 
+// Whether the partition's box waits in shared memory between steps (see the kernel).  Measured on B200: +6 points of
+// FP64 utilisation for the shapes with up to ~50 neurons, -9 for the 100-wide single-hidden-layer shapes.
+template <class S>
+__host__ __device__ constexpr bool fb_profile_smem_box()
+{
+    return FB_PROFILE_SMEM_BOX && S::N <= 64;
+}
+
 // counts[p][N] (uint32): stored when chunks == 1, atomically added otherwise (caller zeroes first).
 template <class S, bool PHILOX>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS, FB_PROFILE_MINB)
@@ -318,14 +332,29 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
         const int c = (int)(u - p * chunks);
         const int s0 = c * chunk_len;
         const int s1 = min(nsamp, s0 + chunk_len);
+        // The box (lo, range per feature) is only needed while a step's samples are drawn.  For most shapes it waits
+        // in shared memory (one copy per warp) and is re-read at the top of every step, instead of holding 2*D0
+        // registers through the network; SMEM_BOX is false for the shapes where that measured slower.
+        constexpr bool SMEM_BOX = fb_profile_smem_box<S>();
+        __shared__ int32_t s_lo[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0 : 1];
+        __shared__ uint32_t s_range[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0 : 1];
         int32_t lo[D0];
         uint32_t range[D0];
         if (PHILOX) {
             const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+            if constexpr (SMEM_BOX) {
+                __syncwarp();
+                for (int i = lane; i < D0; i += 32) {
+                    const int2 b = __ldg(bx + i);
+                    s_lo[threadIdx.x >> 5][i] = b.x; s_range[threadIdx.x >> 5][i] = (uint32_t)(b.y - b.x + 1);
+                }
+                __syncwarp();
+            } else {
 #pragma unroll
-            for (int i = 0; i < D0; ++i) {
-                const int2 b = __ldg(bx + i);
-                lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
+                for (int i = 0; i < D0; ++i) {
+                    const int2 b = __ldg(bx + i);
+                    lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
+                }
             }
         }
         const int64_t pidx = first_index + p;
@@ -342,6 +371,15 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
             bool active[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) active[k] = (sb + 32 * k + lane) < s1;
+            if constexpr (SMEM_BOX) {
+                // one batch of warp-uniform loads per step; the barrier keeps the compiler from hoisting them out
+                // of the loop, which would pin 2*D0 registers again
+                asm volatile("" ::: "memory");
+                if (PHILOX) {
+#pragma unroll
+                    for (int i = 0; i < D0; ++i) { lo[i] = s_lo[threadIdx.x >> 5][i]; range[i] = s_range[threadIdx.x >> 5][i]; }
+                }
+            }
             fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
                                           s1 - 1);
             vis.commit(planes, active);
@@ -357,6 +395,15 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
             FbCountVisit<N, K> vis{cnt};
 #pragma unroll
             for (int k = 0; k < K; ++k) vis.active[k] = (sb + 32 * k + lane) < s1;
+            if constexpr (SMEM_BOX) {
+                // one batch of warp-uniform loads per step; the barrier keeps the compiler from hoisting them out
+                // of the loop, which would pin 2*D0 registers again
+                asm volatile("" ::: "memory");
+                if (PHILOX) {
+#pragma unroll
+                    for (int i = 0; i < D0; ++i) { lo[i] = s_lo[threadIdx.x >> 5][i]; range[i] = s_range[threadIdx.x >> 5][i]; }
+                }
+            }
             fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
                                           s1 - 1);
         }
