@@ -101,7 +101,7 @@ struct FbMaskedVisit {
 // from a generator right where it is consumed (a sample's 13..30 features never sit in registers together).
 // ---------------------------------------------------------------------------------------------------
 #ifndef FB_PROFILE_THREADS
-#define FB_PROFILE_THREADS 256
+#define FB_PROFILE_THREADS 512
 #endif
 #ifndef FB_PROFILE_SPT
 #define FB_PROFILE_SPT 2                                 // samples per lane per step
@@ -117,7 +117,7 @@ struct FbMaskedVisit {
 #define FB_PROFILE_IM 0                                  // 1: input-major forward, 0: output-major (measured best)
 #endif
 #ifndef FB_PROFILE_MINB
-#define FB_PROFILE_MINB 2                                // minimum resident CTAs per SM (caps registers at 128)
+#define FB_PROFILE_MINB 1                                // one 512-thread CTA per SM: caps registers at 128
 #endif
 #define FB_PROFILE_MAX_STEPS (127 / FB_PROFILE_SPT)      // per-lane counters hold up to 127 (7 bit planes)
 
