@@ -11,7 +11,6 @@
 #include "fb_generic.cuh"
 #include "fb_registry.h"
 #include "fb_spec_ops.cuh"
-#include "fb_tiled.cuh"
 
 static_assert(sizeof(fb_prune_out) == sizeof(FbPruneOut), "fb_prune_out and FbPruneOut must match");
 
@@ -62,8 +61,6 @@ struct fb_model {
     float *dW32 = nullptr, *dB32 = nullptr;
     const FbSpecEntry *spec = nullptr;
     void *p64 = nullptr, *p32 = nullptr;
-    TiledNet tiled{};
-    double *dWpad = nullptr;
 };
 
 static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
@@ -85,7 +82,7 @@ extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32);
     delete m;
 }
 
@@ -140,28 +137,6 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         m->p64 = m->spec->make_params64(m->hW64.data(), m->hB64.data());
         m->p32 = m->spec->make_params32(m->hW32.data(), m->hB32.data());
         if (!m->p64 || !m->p32) { fb_model_destroy(m); return fb_fail(FB_ERR_NOMEM, "fb_model_create: out of host memory"); }
-    }
-    // padded copy of the weights for the tiled profile kernel: every row starts 16-byte aligned
-    {
-        TiledNet &t = m->tiled;
-        t.L = L; t.N = g.N; t.P = g.P; t.d = dims[0]; t.wA = 1; t.wB = 1;
-        int po = 0;
-        for (int l = 0; l <= L; ++l) t.dims[l] = dims[l];
-        for (int l = 0; l < L; ++l) {
-            t.ld[l] = (dims[l + 1] + 1) & ~1; t.woff[l] = po; t.boff[l] = g.boff[l];
-            po += dims[l] * t.ld[l];
-            if (l % 2 == 0) t.wA = std::max(t.wA, dims[l]); else t.wB = std::max(t.wB, dims[l]);
-        }
-        t.woff[L] = po; t.boff[L] = g.N; t.Ppad = po;
-        std::vector<double> wp((size_t)po, 0.0);
-        for (int l = 0; l < L; ++l)
-            for (int i = 0; i < dims[l]; ++i)
-                for (int j = 0; j < dims[l + 1]; ++j)
-                    wp[(size_t)t.woff[l] + (size_t)i * t.ld[l] + j] = m->hW64[(size_t)g.woff[l] + (size_t)i * dims[l + 1] + j];
-        e = cudaMalloc(&m->dWpad, sizeof(double) * po);
-        if (e == cudaSuccess) e = cudaMemcpy(m->dWpad, wp.data(), sizeof(double) * po, cudaMemcpyHostToDevice);
-        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
-        t.Wpad = m->dWpad; t.B64 = m->dB64;
     }
     *out = m;
     return FB_OK;
@@ -344,38 +319,6 @@ static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const vo
     return FB_OK;
 }
 
-// tiled profile kernel: shared-memory footprint for K samples per lane and THREADS threads per CTA
-static size_t fb_tiled_smem(const TiledNet &t, int K, int threads)
-{
-    size_t b = sizeof(double) * ((size_t)t.Ppad + ((t.N + 1) & ~1));
-    b += sizeof(double) * (size_t)(t.wA + t.wB) * K * threads;
-    b += ((size_t)t.N * threads + 15) & ~(size_t)15;
-    b += sizeof(int2) * (size_t)(threads / 32) * t.d;
-    return b;
-}
-
-template <int K, int THREADS>
-static cudaError_t fb_launch_tiled(const fb_model *m, bool philox, int64_t n, const int32_t *boxes, const int32_t *samples,
-                                   uint64_t seed, int64_t first_index, int S, int chunks, int chunk_len, uint32_t *counts,
-                                   cudaStream_t st)
-{
-    const size_t smem = fb_tiled_smem(m->tiled, K, THREADS);
-    const int64_t ctas = (n * chunks + (THREADS / 32) - 1) / (THREADS / 32);
-    cudaError_t e;
-    if (philox) {
-        auto k = fb_profile_tiled_kernel<K, THREADS, true>;
-        if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-        k<<<fb_grid_for(k, THREADS, smem, ctas, m->num_sms), THREADS, smem, st>>>(m->tiled, n, boxes, samples, seed, first_index,
-                                                                                 S, chunks, chunk_len, counts);
-    } else {
-        auto k = fb_profile_tiled_kernel<K, THREADS, false>;
-        if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-        k<<<fb_grid_for(k, THREADS, smem, ctas, m->num_sms), THREADS, smem, st>>>(m->tiled, n, boxes, samples, seed, first_index,
-                                                                                 S, chunks, chunk_len, counts);
-    }
-    return cudaGetLastError();
-}
-
 static size_t fb_profile_gen_smem(const fb_model *m)
 {
     return sizeof(double) * ((size_t)m->gen.P + m->gen.N) + sizeof(uint32_t) * (FB_PROFILE_THREADS / 32) * m->gen.N;
@@ -391,33 +334,10 @@ extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, co
     int chunks, chunk_len;
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
     if (chunks > 1) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));
-    static const bool prefer_tiled = [] { const char *v = getenv("FAIRIFY_B200_TILED_PROFILE"); return v && v[0] == '1'; }();
-    if (fb_use_spec(m) && !prefer_tiled) {
+    if (fb_use_spec(m)) {
         FB_CUDA(m->spec->profile(m->p64, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks, chunk_len,
                                  counts, m->num_sms, st));
         return FB_OK;
-    }
-    // runtime-shape path: the tiled kernel with the largest configuration whose shared memory fits; the plain
-    // kernel below only for networks whose weights alone do not leave room (BM-4)
-    {
-        const bool ph = samples == nullptr;
-        const size_t lim = 200 * 1024;
-        if (fb_tiled_smem(m->tiled, 2, 128) <= 72 * 1024) {
-            FB_CUDA((fb_launch_tiled<2, 128>(m, ph, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, st)));
-            return FB_OK;
-        }
-        if (fb_tiled_smem(m->tiled, 2, 64) <= lim) {
-            FB_CUDA((fb_launch_tiled<2, 64>(m, ph, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, st)));
-            return FB_OK;
-        }
-        if (fb_tiled_smem(m->tiled, 1, 64) <= lim) {
-            FB_CUDA((fb_launch_tiled<1, 64>(m, ph, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, st)));
-            return FB_OK;
-        }
-        if (fb_tiled_smem(m->tiled, 1, 32) <= lim) {
-            FB_CUDA((fb_launch_tiled<1, 32>(m, ph, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, st)));
-            return FB_OK;
-        }
     }
     const size_t smem = fb_profile_gen_smem(m);
     if (smem > 227 * 1024) return fb_fail(FB_ERR_UNSUPPORTED, "fb_profile: model needs %zu bytes of shared memory", smem);
