@@ -394,3 +394,22 @@ def test_grid_locate_and_density(eng, tag):
     p_list = partitioned_ranges(rd.keys(), D.pa, partition(rd, T), rd)
     df = pd.DataFrame(np.column_stack([X, np.zeros(len(X), dtype=np.int64)]), columns=D.columns + [D.label])
     assert p_list_density(D.copy_ranges(), p_list, df) == list(z[f"{tag}/density"])
+
+
+def test_result_persistence_roundtrip(eng, tmp_path):
+    from fairify_b200 import persist
+    w, b = G.wb("GC-4")
+    m = eng.Model(w, b)
+    dom = G.domain("GC-4")
+    grid = eng.Grid(dom.columns, dom.ranges, 10)
+    first, n = 1000, 2000
+    r = m.prune(grid.boxes(first, n), S=64, seed=9, first_index=first)
+    path = str(tmp_path / "gc4.npz")
+    persist.save(path, m, grid, 64, 9, first, r)
+    back = persist.load(path, m, grid, 64, 9, first, n)
+    for k in ("cand", "b_dead", "dead", "verdict", "counts"):
+        assert np.array_equal(back[k], r.numpy(k))
+    with pytest.raises(ValueError):
+        persist.load(path, m, grid, 64, 10, first, n)                    # other seed
+    with pytest.raises(ValueError):
+        persist.load(path, eng.Model(*G.wb("GC-3")), grid, 64, 9, first, n)   # other model
