@@ -94,11 +94,9 @@ struct FbMaskedVisit {
 // Activation profile.  reference: candidate_dead_nodes, utils/prune.py:168-192 (activation != 0 counted per
 // neuron, output layer included) over the samples of simluate_data (:205-222).
 //
-// One warp per (partition, sample chunk).  Each lane carries K = FB_PROFILE_SPT samples per step, so a step
-// covers 32*K samples.  The forward pass is input-major: acc[j] += w[i][j] * x_i for i ascending -- per
-// output neuron the terms are added in exactly the order of fb_spec_forward / the oracle -- which lets one
-// uniform constant-bank fetch of a weight feed K fused multiply-adds, and lets layer 0 take each feature
-// from a generator right where it is consumed (a sample's 13..30 features never sit in registers together).
+// One warp per (partition, sample chunk).  Each lane carries K samples per step (VecD<K>: 2 where the register
+// budget allows, else 1), so a step covers 32*K samples and every weight fetched from the constant bank feeds K
+// fused multiply-adds.  The network itself is fb_spec_forward (layer-pair fused, terms in ascending input order).
 // ---------------------------------------------------------------------------------------------------
 #ifndef FB_PROFILE_THREADS
 #define FB_PROFILE_THREADS 512
@@ -113,9 +111,6 @@ struct FbMaskedVisit {
 #define FB_PROFILE_SMEM_BOX 1
 #endif
 #define FB_BOX_QUAL const
-#ifndef FB_PROFILE_IM
-#define FB_PROFILE_IM 0                                  // 1: input-major forward, 0: output-major (measured best)
-#endif
 #ifndef FB_PROFILE_MINB
 #define FB_PROFILE_MINB 1                                // one 512-thread CTA per SM: caps registers at 128
 #endif
@@ -189,51 +184,7 @@ struct FbCountVisit {
 #endif
 };
 
-template <class S, int l, typename T, class PRM, class Visit>
-__device__ __forceinline__ void fb_spec_layer_epilogue(const PRM &prm, T (&y)[S::dim(l + 1)], Visit &v)
-{
-    constexpr int OUT = S::dim(l + 1), BO = S::boff(l);
-    constexpr bool last = (l == S::NL - 1);
-#pragma unroll
-    for (int j = 0; j < OUT; ++j) y[j] = v.neuron(BO + j, last, fb_add(y[j], prm.b[BO + j]));
-}
-
-template <class S, int l, typename T, class PRM, class Visit>
-__device__ __forceinline__ T fb_spec_forward_im(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
-{
-    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l);
-    T y[OUT];
-#pragma unroll
-    for (int j = 0; j < OUT; ++j) y[j] = T(0.0);
-#pragma unroll
-    for (int i = 0; i < IN; ++i) {
-#pragma unroll
-        for (int j = 0; j < OUT; ++j) y[j] = fb_fma(prm.w[WO + i * OUT + j], x[i], y[j]);
-    }
-    fb_spec_layer_epilogue<S, l, T>(prm, y, v);
-    if constexpr (l == S::NL - 1) return y[0];
-    else return fb_spec_forward_im<S, l + 1, T, PRM, Visit>(prm, y, v);
-}
-
-template <class S, typename T, class PRM, class Visit, class XGen>
-__device__ __forceinline__ T fb_spec_forward_gen_in(const PRM &prm, XGen &xg, Visit &v)
-{
-    constexpr int IN = S::dim(0), OUT = S::dim(1);
-    T y[OUT];
-#pragma unroll
-    for (int j = 0; j < OUT; ++j) y[j] = T(0.0);
-#pragma unroll
-    for (int i = 0; i < IN; ++i) {
-        const T xi = xg.feature(i);
-#pragma unroll
-        for (int j = 0; j < OUT; ++j) y[j] = fb_fma(prm.w[i * OUT + j], xi, y[j]);
-    }
-    fb_spec_layer_epilogue<S, 0, T>(prm, y, v);
-    if constexpr (S::NL == 1) return y[0];
-    else return fb_spec_forward_im<S, 1, T, PRM, Visit>(prm, y, v);
-}
-
-// layer-0 input generators: feature(i) is called for i = 0, 1, ... in order
+// sources of a step's samples: feature(i) is called for i = 0, 1, ... in order
 template <int D0, int K>
 struct FbPhiloxGen {
     FB_BOX_QUAL int32_t (&lo)[D0];
@@ -276,22 +227,19 @@ __device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm
                                                 int64_t pidx, uint64_t seed, int s_clamp = 0x7fffffff)
 {
     constexpr int D0 = S::D0;
+    VecD<K> x[D0];
     if (PHILOX) {
         FbPhiloxGen<D0, K> xg{lo, range, s, pidx, seed};
-#if FB_PROFILE_IM
-        fb_spec_forward_gen_in<S, VecD<K>>(prm, xg, vis);
-#else
-        VecD<K> x[D0];
 #pragma unroll
         for (int i = 0; i < D0; ++i) x[i] = xg.feature(i);
-        fb_spec_forward<S, 0, VecD<K>>(prm, x, vis);
-#endif
     } else {
         FbInjectGen<D0, K> xg;
 #pragma unroll
         for (int k = 0; k < K; ++k) xg.row[k] = part_samples + (int64_t)min(s + 32 * k, s_clamp) * D0;
-        fb_spec_forward_gen_in<S, VecD<K>>(prm, xg, vis);
+#pragma unroll
+        for (int i = 0; i < D0; ++i) x[i] = xg.feature(i);
     }
+    fb_spec_forward<S, 0, VecD<K>>(prm, x, vis);
 }
 
 // Samples per lane for shape S: FB_PROFILE_SPT (2) when the live state of the widest layer pair -- the inputs of
