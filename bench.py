@@ -325,8 +325,10 @@ def run_gpu(args):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "host_equals_device": same},
-        "gpu_launches": 2 * args.steps,
-        "roofline": {"kernel": "fb_profile_spec_kernel<Spec<13,16,8,1>, philox>", "bound": "fp64", "achieved": achieved,
+        "gpu_launches": 4 * args.steps,         # per step: the profile kernel once per draw class (3) + bounds/masks (1)
+        "roofline": {"kernel": "fb_profile_spec_kernel<Spec<13,16,8,1>, philox, 4 features per word> (kernel_ms also holds the two "
+                               "launches for the other draw classes, which find no partition of theirs in this grid)",
+                     "bound": "fp64", "achieved": achieved,
                      "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": traffic,
                      "peak_source": "measured in this run: fb_fp64_peak (DFMA issue-rate microbenchmark, FMA = 2 flops); "
                                     "MEASURED_PEAKS.json has no FP64 figure; nominal 148 SM x 64 lanes x 1.965 GHz x 2 = 37.2",

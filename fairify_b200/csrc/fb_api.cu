@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <mutex>
 #include <vector>
 
 #include "../../include/fairify_b200.h"
@@ -407,6 +408,25 @@ struct DevBuf {
 };
 }  // namespace
 
+// Copy streams of fb_prune_host, one pair per device, created on first use and kept.
+static int fb_copy_streams(int device, cudaStream_t *up, cudaStream_t *down)
+{
+    static cudaStream_t s_up[64] = {}, s_down[64] = {};
+    static std::mutex mu;
+    if (device < 0 || device >= 64) return fb_fail(FB_ERR_UNSUPPORTED, "fb_prune_host: device ordinal %d", device);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!s_up[device]) {
+        FB_CUDA(cudaStreamCreateWithFlags(&s_up[device], cudaStreamNonBlocking));
+        FB_CUDA(cudaStreamCreateWithFlags(&s_down[device], cudaStreamNonBlocking));
+    }
+    *up = s_up[device]; *down = s_down[device];
+    return FB_OK;
+}
+
+// Partitions per slice of the host pipeline: big enough that a slice fills the GPU many times over, small enough
+// that the first upload and the last download (the only copies not hidden behind compute) are short.
+#define FB_HOST_SLICE 1000000
+
 extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                              uint64_t seed, int64_t first_index, const double *tol, const fb_prune_out *out, void *stream)
 {
@@ -416,43 +436,84 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
     cudaStream_t st = (cudaStream_t)stream;
     const int N = m->gen.N, NW = (N + 31) / 32, d = m->gen.dims[0];
     fb_pool_keep_cached(m->device);
+    cudaStream_t up, down;
+    if (int rc = fb_copy_streams(m->device, &up, &down)) return rc;
+
+    // device copies of the inputs and one device buffer per requested output (whole batch; freed on `st` at return)
     DevBuf dboxes(st), dsamp(st), dtol(st);
     FB_CUDA(dboxes.alloc(sizeof(int32_t) * n * d * 2));
-    FB_CUDA(cudaMemcpyAsync(dboxes.p, boxes, sizeof(int32_t) * n * d * 2, cudaMemcpyHostToDevice, st));
-    if (samples) {
-        FB_CUDA(dsamp.alloc(sizeof(int32_t) * n * S * d));
-        FB_CUDA(cudaMemcpyAsync(dsamp.p, samples, sizeof(int32_t) * n * S * d, cudaMemcpyHostToDevice, st));
-    }
+    if (samples) FB_CUDA(dsamp.alloc(sizeof(int32_t) * n * S * d));
     if (tol) {
         FB_CUDA(dtol.alloc(sizeof(double) * N));
         FB_CUDA(cudaMemcpyAsync(dtol.p, tol, sizeof(double) * N, cudaMemcpyHostToDevice, st));
     }
-    // one device buffer per requested output
-    struct Slot { void *host; size_t bytes; void **dev_field; };
+    struct Slot { void *host; size_t row_bytes; void **dev_field; void *dev; };
     fb_prune_out dev{};
-    const size_t mb = sizeof(uint32_t) * n * NW, fb = sizeof(double) * n * N;
+    const size_t mb = sizeof(uint32_t) * NW, fb = sizeof(double) * N;
     Slot slots[] = {
-        {out->cand, mb, (void **)&dev.cand},     {out->b_dead, mb, (void **)&dev.b_dead},
-        {out->dead, mb, (void **)&dev.dead},     {out->sliver, mb, (void **)&dev.sliver},
-        {out->verdict, (size_t)n, (void **)&dev.verdict}, {out->counts, sizeof(uint16_t) * n * N, (void **)&dev.counts},
-        {out->ws_lb, fb, (void **)&dev.ws_lb},   {out->ws_ub, fb, (void **)&dev.ws_ub},
-        {out->pl_lb, fb, (void **)&dev.pl_lb},   {out->pl_ub, fb, (void **)&dev.pl_ub},
-        {out->lb_rd, fb, (void **)&dev.lb_rd},   {out->ub_ru, fb, (void **)&dev.ub_ru},
+        {out->cand, mb, (void **)&dev.cand, nullptr},     {out->b_dead, mb, (void **)&dev.b_dead, nullptr},
+        {out->dead, mb, (void **)&dev.dead, nullptr},     {out->sliver, mb, (void **)&dev.sliver, nullptr},
+        {out->verdict, 1, (void **)&dev.verdict, nullptr}, {out->counts, sizeof(uint16_t) * N, (void **)&dev.counts, nullptr},
+        {out->ws_lb, fb, (void **)&dev.ws_lb, nullptr},   {out->ws_ub, fb, (void **)&dev.ws_ub, nullptr},
+        {out->pl_lb, fb, (void **)&dev.pl_lb, nullptr},   {out->pl_ub, fb, (void **)&dev.pl_ub, nullptr},
+        {out->lb_rd, fb, (void **)&dev.lb_rd, nullptr},   {out->ub_ru, fb, (void **)&dev.ub_ru, nullptr},
     };
     std::vector<DevBuf> bufs;
     bufs.reserve(sizeof(slots) / sizeof(slots[0]));
     for (Slot &s : slots) {
         if (!s.host) continue;
         bufs.emplace_back(st);
-        FB_CUDA(bufs.back().alloc(s.bytes));
-        *s.dev_field = bufs.back().p;
+        FB_CUDA(bufs.back().alloc(s.row_bytes * n));
+        s.dev = bufs.back().p;
     }
-    int rc = fb_prune(m, n, (const int32_t *)dboxes.p, (const int32_t *)dsamp.p, S, seed, first_index,
-                      (const double *)dtol.p, &dev, stream);
+
+    // Three-stage pipeline over slices of the batch: upload on `up`, kernels on the caller's stream, download on
+    // `down`; slice k's kernels overlap slice k+1's upload and slice k-1's download.  Results do not depend on the
+    // slicing (every partition's samples are a function of its global index only).
+    struct Events {
+        std::vector<cudaEvent_t> v;
+        ~Events() { for (cudaEvent_t e : v) cudaEventDestroy(e); }
+        cudaError_t make(cudaEvent_t *e)
+        {
+            cudaError_t rc = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
+            if (rc == cudaSuccess) v.push_back(*e);
+            return rc;
+        }
+    } events;
+    cudaEvent_t ready;                                   // allocations (and tol) are in place on `st`
+    FB_CUDA(events.make(&ready));
+    FB_CUDA(cudaEventRecord(ready, st));
+    FB_CUDA(cudaStreamWaitEvent(up, ready, 0));
+    FB_CUDA(cudaStreamWaitEvent(down, ready, 0));
+    int rc = FB_OK;
+    for (int64_t off = 0; off < n && rc == FB_OK; off += FB_HOST_SLICE) {
+        const int64_t cnt = std::min<int64_t>(FB_HOST_SLICE, n - off);
+        cudaEvent_t uploaded, computed;
+        FB_CUDA(events.make(&uploaded));
+        FB_CUDA(events.make(&computed));
+        int32_t *bx = (int32_t *)dboxes.p + off * d * 2;
+        FB_CUDA(cudaMemcpyAsync(bx, boxes + off * d * 2, sizeof(int32_t) * cnt * d * 2, cudaMemcpyHostToDevice, up));
+        int32_t *sm = nullptr;
+        if (samples) {
+            sm = (int32_t *)dsamp.p + off * S * d;
+            FB_CUDA(cudaMemcpyAsync(sm, samples + off * S * d, sizeof(int32_t) * cnt * S * d, cudaMemcpyHostToDevice, up));
+        }
+        FB_CUDA(cudaEventRecord(uploaded, up));
+        FB_CUDA(cudaStreamWaitEvent(st, uploaded, 0));
+        for (Slot &s : slots) *s.dev_field = s.dev ? (char *)s.dev + s.row_bytes * off : nullptr;
+        rc = fb_prune(m, cnt, bx, sm, S, seed, first_index + off, (const double *)dtol.p, &dev, stream);
+        if (rc != FB_OK) break;
+        FB_CUDA(cudaEventRecord(computed, st));
+        FB_CUDA(cudaStreamWaitEvent(down, computed, 0));
+        for (Slot &s : slots)
+            if (s.host)
+                FB_CUDA(cudaMemcpyAsync((char *)s.host + s.row_bytes * off, (char *)s.dev + s.row_bytes * off,
+                                        s.row_bytes * cnt, cudaMemcpyDeviceToHost, down));
+    }
+    // everything issued must finish before the buffers are released (also on the error path)
+    cudaError_t e1 = cudaStreamSynchronize(up), e2 = cudaStreamSynchronize(st), e3 = cudaStreamSynchronize(down);
     if (rc != FB_OK) return rc;
-    for (Slot &s : slots)
-        if (s.host) FB_CUDA(cudaMemcpyAsync(s.host, *s.dev_field, s.bytes, cudaMemcpyDeviceToHost, st));
-    FB_CUDA(cudaStreamSynchronize(st));
+    FB_CUDA(e1); FB_CUDA(e2); FB_CUDA(e3);
     return FB_OK;
 }
 

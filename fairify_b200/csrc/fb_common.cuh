@@ -20,7 +20,7 @@
 #define FB_WARP 32
 
 // ---------------------------------------------------------------------------------------------------
-// Philox4x32-10, counter = (sample, partition_lo, partition_hi, feature/4), key = (seed_lo, seed_hi).
+// Philox4x32-10, counter = (sample, partition_lo, partition_hi, block), key = (seed_lo, seed_hi).
 // Bit-identical to philox4x32_10() in the oracle.
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void fb_philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
@@ -44,10 +44,63 @@ __device__ __forceinline__ void fb_philox4x32_10(uint32_t c0, uint32_t c1, uint3
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-// value in [lo, lo+range) from one 32-bit word
-__device__ __forceinline__ int32_t fb_map_range(uint32_t word, int32_t lo, uint32_t range)
+// ---------------------------------------------------------------------------------------------------
+// Bounded integers from Philox words.  A feature with `range` values takes the high half of word * range; the
+// low half of that product is again a uniform 32-bit word (up to a relative bias of range / 2^32), so it can
+// serve the next feature -- the batched form of the multiply-shift method.  How many features share one word
+// (G) depends on the partition's widest feature range, so that the product of the ranges drawn from one word
+// never exceeds 2^16 and every value's probability stays within 2^-16 (relative) of uniform:
+//   widest range <= 16  -> G = 4,   <= 256 -> G = 2,   otherwise G = 1 (one word per feature).
+// Feature i uses word i / G of the sample's word stream; word q is output q % 4 of the Philox block with
+// counter (sample, partition_lo, partition_hi, q / 4).  Identical in the oracle (fo_sample_row).
+// ---------------------------------------------------------------------------------------------------
+#define FB_DRAW4_MAX_RANGE 16u
+#define FB_DRAW2_MAX_RANGE 256u
+__host__ __device__ __forceinline__ int fb_draw_group(uint32_t widest_range)
 {
-    return lo + (int32_t)__umulhi(word, range);
+    return widest_range <= FB_DRAW4_MAX_RANGE ? 4 : (widest_range <= FB_DRAW2_MAX_RANGE ? 2 : 1);
+}
+
+// one feature: value in [lo, lo + range), and the word handed on to the next feature of the group
+__device__ __forceinline__ int32_t fb_draw_next(uint32_t &word, int32_t lo, uint32_t range)
+{
+    const uint64_t prod = (uint64_t)word * range;
+    word = (uint32_t)prod;
+    return lo + (int32_t)(uint32_t)(prod >> 32);
+}
+
+// Runtime-width form: all D0 features of sample s of partition pidx; box = this partition's (lo, hi) pairs.
+// OUT is double or float.
+template <typename OUT>
+__device__ __forceinline__ void fb_draw_row(const int32_t *__restrict__ box, int D0, int G, uint32_t s, int64_t pidx,
+                                            uint64_t seed, OUT *x)
+{
+    const int nwords = (D0 + G - 1) / G;
+    for (int blk = 0; blk * 4 < nwords; ++blk) {
+        uint32_t r[4];
+        fb_philox4x32_10(s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk, (uint32_t)seed,
+                         (uint32_t)(seed >> 32), r);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t word = r[k];
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int i = (blk * 4 + k) * G + g;
+                if (g < G && i < D0) {
+                    const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
+                    x[i] = (OUT)fb_draw_next(word, lo, (uint32_t)(hi - lo + 1));
+                }
+            }
+        }
+    }
+}
+
+// widest feature range of a box (every lane computes the same value)
+__device__ __forceinline__ uint32_t fb_box_widest(const int32_t *__restrict__ box, int D0)
+{
+    uint32_t widest = 0;
+    for (int i = 0; i < D0; ++i) widest = max(widest, (uint32_t)(__ldg(box + 2 * i + 1) - __ldg(box + 2 * i) + 1));
+    return widest;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -64,13 +117,31 @@ struct Spec {
     static constexpr int N = boff(NL);
     static constexpr int D0 = dim(0);
     static constexpr int NW = (N + 31) / 32;              // mask words per partition
+    // Position of weight (input i -> neuron j) of layer l inside SpecParams::w.  Even layers are stored [out][in],
+    // odd layers [in][out] (the Keras layout): fb_spec_forward walks an even layer neuron by neuron over ascending
+    // inputs and folds each finished neuron into all accumulators of the following odd layer, so in both cases the
+    // weights it needs next are neighbours in the constant bank and arrive two per 128-bit uniform load.
+    __host__ __device__ static constexpr int widx(int l, int i, int j)
+    {
+        return (l & 1) ? woff(l) + i * dim(l + 1) + j : woff(l) + j * dim(l) + i;
+    }
 };
 
 template <class S, typename T>
 struct SpecParams {
-    T w[S::P];      // layer-major, each [in][out] row-major (Keras kernel layout)
+    T w[S::P];      // layer-major, element order given by S::widx (filled by fb_spec_fill from the Keras layout)
     T b[S::N];
 };
+
+// host: copy a model given layer-major with [in][out] row-major kernels (what Keras get_weights() returns)
+template <class S, typename T>
+static inline void fb_spec_fill(SpecParams<S, T> &p, const T *W, const T *B)
+{
+    for (int l = 0; l < S::NL; ++l)
+        for (int i = 0; i < S::dim(l); ++i)
+            for (int j = 0; j < S::dim(l + 1); ++j) p.w[S::widx(l, i, j)] = W[S::woff(l) + i * S::dim(l + 1) + j];
+    for (int k = 0; k < S::N; ++k) p.b[k] = B[k];
+}
 
 // ---------------------------------------------------------------------------------------------------
 // Runtime network shape (generic path).  W64/W32 point at device copies with the same layout as above.

@@ -106,24 +106,13 @@ fb_profile_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ b
         __syncwarp();
         const int32_t *box = boxes + p * (2 * D0);
         const int64_t pidx = first_index + p;
+        const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
         FbGenCountVisit vis{cnt, false, lane};
         for (int sb = s0; sb < s1; sb += 32) {
             const int s = sb + lane;
             vis.active = s < s1;
             if (PHILOX) {
-                for (int blk = 0; blk * 4 < D0; ++blk) {
-                    uint32_t r[4];
-                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
-                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int i = blk * 4 + k;
-                        if (i < D0) {
-                            const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
-                            a[i] = (double)fb_map_range(r[k], lo, (uint32_t)(hi - lo + 1));
-                        }
-                    }
-                }
+                fb_draw_row<double>(box, D0, grp, (uint32_t)s, pidx, seed, a);
             } else {
                 const int32_t *row = samples + ((int64_t)p * nsamp + (vis.active ? s : s0)) * D0;
                 for (int i = 0; i < D0; ++i) a[i] = (double)__ldg(row + i);
@@ -318,24 +307,13 @@ fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__res
         const int32_t *box = boxes + p * (2 * D0);
         const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
         const int64_t pidx = first_index + p;
+        const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
         unsigned long long best = ~0ull;
         for (int sb = s0; sb < s1; sb += 32) {
             const int s = sb + lane;
             const bool active = s < s1;
             if (PHILOX) {
-                for (int blk = 0; blk * 4 < D0; ++blk) {
-                    uint32_t r[4];
-                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
-                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int i = blk * 4 + k;
-                        if (i < D0) {
-                            const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
-                            x0[i] = (float)fb_map_range(r[k], lo, (uint32_t)(hi - lo + 1));
-                        }
-                    }
-                }
+                fb_draw_row<float>(box, D0, grp, (uint32_t)s, pidx, seed, x0);
             } else {
                 const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
                 for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);

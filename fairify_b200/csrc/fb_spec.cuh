@@ -21,41 +21,40 @@
 // inputs of layer l plus the accumulators of layer l+1 -- e.g. 13 + 1 values for a 13-100-1 network instead
 // of 13 + 100.
 #ifndef FB_SPEC_JB
-#define FB_SPEC_JB 1            // neurons of layer l evaluated together (1 measured best; 2-8 need more registers than they save)
+#define FB_SPEC_JB 1
 #endif
 template <class S, int l, typename T, class PRM, class Visit>
 __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
 {
-    constexpr int IN = S::dim(l), M = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
+    constexpr int IN = S::dim(l), M = S::dim(l + 1), BO = S::boff(l);
     constexpr bool has_next = (l + 1 < S::NL);
     constexpr int L2 = has_next ? l + 1 : l;                      // (kept in range when there is no next layer)
-    constexpr int M2 = has_next ? S::dim(L2 + 1) : 1, WO2 = S::woff(L2), BO2 = S::boff(L2);
+    constexpr int M2 = has_next ? S::dim(L2 + 1) : 1, BO2 = S::boff(L2);
     T acc2[M2];
 #pragma unroll
     for (int k = 0; k < M2; ++k) acc2[k] = T(0.0);
     T h = T(0.0);
-    // neurons of layer l in blocks of FB_SPEC_JB: inside a block the inputs are walked once and each x_i feeds
-    // JB independent accumulators whose weights w[i][j0 .. j0+JB) are adjacent in the constant bank (one wide
-    // uniform load per pair), which gives the FP64 pipe JB * K independent chains instead of K
+    // neurons of layer l in blocks of JB (independent dot products side by side).  Measured on B200: 1, 2, 4 and 8
+    // give the same rate -- ptxas interleaves neighbouring neurons' chains by itself -- so 1 it stays.
+    constexpr int JB = FB_SPEC_JB;
 #pragma unroll
-    for (int j0 = 0; j0 < M; j0 += FB_SPEC_JB) {
-        constexpr int JBmax = FB_SPEC_JB;
-        T acc[JBmax];
+    for (int j0 = 0; j0 < M; j0 += JB) {
+        T acc[JB];
 #pragma unroll
-        for (int jj = 0; jj < JBmax; ++jj) acc[jj] = T(0.0);
+        for (int jj = 0; jj < JB; ++jj) acc[jj] = T(0.0);
 #pragma unroll
         for (int i = 0; i < IN; ++i) {
 #pragma unroll
-            for (int jj = 0; jj < JBmax; ++jj)
-                if (j0 + jj < M) acc[jj] = fb_fma(prm.w[WO + i * M + j0 + jj], x[i], acc[jj]);
+            for (int jj = 0; jj < JB; ++jj)
+                if (j0 + jj < M) acc[jj] = fb_fma(prm.w[S::widx(l, i, j0 + jj)], x[i], acc[jj]);
         }
 #pragma unroll
-        for (int jj = 0; jj < JBmax; ++jj) {
+        for (int jj = 0; jj < JB; ++jj) {
             if (j0 + jj < M) {
                 h = v.neuron(BO + j0 + jj, !has_next, fb_add(acc[jj], prm.b[BO + j0 + jj]));
                 if constexpr (has_next) {
 #pragma unroll
-                    for (int k = 0; k < M2; ++k) acc2[k] = fb_fma(prm.w[WO2 + (j0 + jj) * M2 + k], h, acc2[k]);
+                    for (int k = 0; k < M2; ++k) acc2[k] = fb_fma(prm.w[S::widx(L2, j0 + jj, k)], h, acc2[k]);
                 }
             }
         }
@@ -110,21 +109,15 @@ struct FbMaskedVisit {
 #ifndef FB_PROFILE_SMEM_BOX
 #define FB_PROFILE_SMEM_BOX 1
 #endif
-#define FB_BOX_QUAL const
 #ifndef FB_PROFILE_MINB
 #define FB_PROFILE_MINB 1                                // one 512-thread CTA per SM: caps registers at 128
 #endif
 #define FB_PROFILE_MAX_STEPS (127 / FB_PROFILE_SPT)      // per-lane counters hold up to 127 (7 bit planes)
 
-// per-lane packed 8-bit counters, one field per neuron
-#ifndef FB_PROFILE_BITSLICE
-#define FB_PROFILE_BITSLICE 1        // 1: per-sample non-zero bit masks + bit-sliced counters, 0: packed 8-bit counters
-#endif
 #define FB_PROFILE_PLANES 7          // bit-sliced counters count to 127 per lane
 
 template <int N, int K>
 struct FbCountVisit {
-#if FB_PROFILE_BITSLICE
     // One bit per neuron and sample: neuron idx sets bit idx of nzmask[k].  After the forward pass the masks
     // are added into `planes`, a bit-sliced counter (planes[b] holds bit b of every neuron's count): two
     // logic ops per plane add one sample to ALL neurons' counters at once, and the activity flag of a ragged
@@ -166,78 +159,56 @@ struct FbCountVisit {
                 }
             }
     }
-#else
-    uint32_t (&cnt)[(N + 3) / 4];
-    bool active[K];             // false for sample slots past the end of the chunk (ragged last step)
-    __device__ __forceinline__ VecD<K> neuron(int idx, bool last, const VecD<K> &pre)
-    {
-        VecD<K> r;
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const bool pos = fb_pos(pre.v[k]);
-            const bool nz = last ? fb_nonzero(pre.v[k]) : pos;
-            if (nz && active[k]) cnt[idx >> 2] += 1u << (8 * (idx & 3));
-            r.v[k] = last ? pre.v[k] : (pos ? pre.v[k] : 0.0);
-        }
-        return r;
-    }
-#endif
 };
 
-// sources of a step's samples: feature(i) is called for i = 0, 1, ... in order
-template <int D0, int K>
-struct FbPhiloxGen {
-    FB_BOX_QUAL int32_t (&lo)[D0];
-    FB_BOX_QUAL uint32_t (&range)[D0];
-    int s;                      // this lane's first sample of the step; its k-th sample is s + 32*k
-    int64_t pidx;
-    uint64_t seed;
+// Compile-time-width form of fb_draw_row: features of the K samples s, s+32, ... of partition pidx, G features per
+// Philox word (G = fb_draw_group of the box, warp-uniform).
+template <int K>
+__device__ __forceinline__ void fb_draw_put(VecD<K> &x, int k, int32_t val) { x.v[k] = (double)val; }
+__device__ __forceinline__ void fb_draw_put(float &x, int, int32_t val) { x = (float)val; }
+
+template <int D0, int K, int G, class X>
+__device__ __forceinline__ void fb_draw_spec(const int32_t (&lo)[D0], const uint32_t (&range)[D0], int s, int64_t pidx,
+                                             uint64_t seed, X (&x)[D0])
+{
+    constexpr int NWORDS = (D0 + G - 1) / G;
     uint32_t r[K][4];
-    __device__ __forceinline__ VecD<K> feature(int i)
-    {
-        if ((i & 3) == 0) {
+#pragma unroll
+    for (int q = 0; q < NWORDS; ++q) {
+        if ((q & 3) == 0) {
 #pragma unroll
             for (int k = 0; k < K; ++k)
                 fb_philox4x32_10((uint32_t)(s + 32 * k), (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32),
-                                 (uint32_t)(i >> 2), (uint32_t)seed, (uint32_t)(seed >> 32), r[k]);
+                                 (uint32_t)(q >> 2), (uint32_t)seed, (uint32_t)(seed >> 32), r[k]);
         }
-        VecD<K> x;
 #pragma unroll
-        for (int k = 0; k < K; ++k) x.v[k] = (double)fb_map_range(r[k][i & 3], lo[i], range[i]);
-        return x;
-    }
-};
-
-template <int D0, int K>
-struct FbInjectGen {
-    const int32_t *row[K];
-    __device__ __forceinline__ VecD<K> feature(int i)
-    {
-        VecD<K> x;
+        for (int k = 0; k < K; ++k) {
+            uint32_t word = r[k][q & 3];
 #pragma unroll
-        for (int k = 0; k < K; ++k) x.v[k] = (double)__ldg(row[k] + i);
-        return x;
+            for (int g = 0; g < G; ++g)
+                if (q * G + g < D0) fb_draw_put(x[q * G + g], k, fb_draw_next(word, lo[q * G + g], range[q * G + g]));
+        }
     }
-};
+}
 
 // one step of the profile: this lane's K samples (indices s, s+32, ...) through the whole network
-template <class S, int K, bool PHILOX, class Visit>
-__device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm, Visit &vis, FB_BOX_QUAL int32_t (&lo)[S::D0],
-                                                FB_BOX_QUAL uint32_t (&range)[S::D0], const int32_t *part_samples, int s,
+template <class S, int K, bool PHILOX, int G, class Visit>
+__device__ __forceinline__ void fb_profile_step(const SpecParams<S, double> &prm, Visit &vis, const int32_t (&lo)[S::D0],
+                                                const uint32_t (&range)[S::D0], const int32_t *part_samples, int s,
                                                 int64_t pidx, uint64_t seed, int s_clamp = 0x7fffffff)
 {
     constexpr int D0 = S::D0;
     VecD<K> x[D0];
     if (PHILOX) {
-        FbPhiloxGen<D0, K> xg{lo, range, s, pidx, seed};
-#pragma unroll
-        for (int i = 0; i < D0; ++i) x[i] = xg.feature(i);
+        fb_draw_spec<D0, K, G>(lo, range, s, pidx, seed, x);
     } else {
-        FbInjectGen<D0, K> xg;
+        const int32_t *row[K];
 #pragma unroll
-        for (int k = 0; k < K; ++k) xg.row[k] = part_samples + (int64_t)min(s + 32 * k, s_clamp) * D0;
+        for (int k = 0; k < K; ++k) row[k] = part_samples + (int64_t)min(s + 32 * k, s_clamp) * D0;
 #pragma unroll
-        for (int i = 0; i < D0; ++i) x[i] = xg.feature(i);
+        for (int i = 0; i < D0; ++i)
+#pragma unroll
+            for (int k = 0; k < K; ++k) x[i].v[k] = (double)__ldg(row[k] + i);
     }
     fb_spec_forward<S, 0, VecD<K>>(prm, x, vis);
 }
@@ -263,19 +234,69 @@ __host__ __device__ constexpr bool fb_profile_smem_box()
     return FB_PROFILE_SMEM_BOX && S::N <= 64;
 }
 
+// all steps of one (partition, sample chunk): samples [s0, s1), 32*K per step, counted into the bit-sliced planes
+template <class S, int K, bool PHILOX, int G, bool SMEM_BOX>
+__device__ __forceinline__ void fb_profile_steps(const SpecParams<S, double> &prm,
+                                                 uint32_t (&planes)[FB_PROFILE_PLANES][(S::N + 31) / 32],
+                                                 const int32_t (&lo)[S::D0], const uint32_t (&range)[S::D0],
+                                                 const int32_t *smem_lo, const uint32_t *smem_range,
+                                                 const int32_t *part_samples, int s0, int s1, int lane, int64_t pidx,
+                                                 uint64_t seed)
+{
+    for (int sb = s0; sb < s1; sb += 32 * K) {
+        FbCountVisit<S::N, K> vis;
+        vis.begin();
+        bool active[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) active[k] = (sb + 32 * k + lane) < s1;
+        // The barrier keeps loop-invariant loads inside the step.  Without it the compiler hoists constant-bank weight
+        // loads (and the shared-memory box) out of the sample loop, runs out of uniform registers and spills them.
+        asm volatile("" ::: "memory");
+        if constexpr (SMEM_BOX && PHILOX) {
+            int32_t rlo[S::D0];
+            uint32_t rrange[S::D0];
+#pragma unroll
+            for (int i = 0; i < S::D0; ++i) { rlo[i] = smem_lo[i]; rrange[i] = smem_range[i]; }
+            fb_profile_step<S, K, PHILOX, G>(prm, vis, rlo, rrange, part_samples, sb + lane, pidx, seed, s1 - 1);
+        } else
+            fb_profile_step<S, K, PHILOX, G>(prm, vis, lo, range, part_samples, sb + lane, pidx, seed, s1 - 1);
+        vis.commit(planes, active);
+    }
+}
+
 // counts[p][N] (uint32): stored when chunks == 1, atomically added otherwise (caller zeroes first).
-template <class S, bool PHILOX>
+//
+// With PHILOX the kernel exists once per draw class G and a launch handles exactly the partitions whose box has that
+// class (the launcher runs G = 4, 2, 1 one after the other; every partition is taken by one of them).  Work is handed
+// out in blocks of `ublock` (1 or 32) consecutive units: lane t classifies unit t of the block, so skipping a block
+// that belongs to another launch costs one round of loads per 32 partitions.
+template <class S, bool PHILOX, int G>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS, FB_PROFILE_MINB)
 fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
                        const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
-                       int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *__restrict__ counts)
+                       int64_t first_index, int nsamp, int chunks, int chunk_len, int ublock,
+                       uint32_t *__restrict__ counts)
 {
     constexpr int D0 = S::D0, N = S::N, K = fb_profile_spt<S>();
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t units = n * chunks;
-    for (int64_t u = gwarp; u < units; u += nwarps) {
+    const int64_t ublocks = (units + ublock - 1) / ublock;
+    int64_t ub = gwarp, ubase = 0;                    // next block to classify; first unit of the block being worked on
+    uint32_t todo = 0;                                // units of that block still to do
+    for (;;) {
+        while (todo == 0) {
+            if (ub >= ublocks) return;
+            ubase = ub * ublock;
+            const int64_t ut = ubase + lane;
+            bool mine = lane < ublock && ut < units;
+            if (PHILOX && mine) mine = fb_draw_group(fb_box_widest(boxes + (ut / chunks) * (2 * D0), D0)) == G;
+            todo = __ballot_sync(0xffffffffu, mine);
+            ub += nwarps;
+        }
+        const int64_t u = ubase + (__ffs(todo) - 1);
+        todo &= todo - 1;
         const int64_t p = u / chunks;
         const int c = (int)(u - p * chunks);
         const int s0 = c * chunk_len;
@@ -306,73 +327,28 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
             }
         }
         const int64_t pidx = first_index + p;
-#if FB_PROFILE_BITSLICE
         constexpr int NWm = (N + 31) / 32;
         uint32_t planes[FB_PROFILE_PLANES][NWm];
 #pragma unroll
         for (int b = 0; b < FB_PROFILE_PLANES; ++b)
 #pragma unroll
             for (int w = 0; w < NWm; ++w) planes[b][w] = 0;
-        for (int sb = s0; sb < s1; sb += 32 * K) {
-            FbCountVisit<N, K> vis;
-            vis.begin();
-            bool active[K];
-#pragma unroll
-            for (int k = 0; k < K; ++k) active[k] = (sb + 32 * k + lane) < s1;
-            if constexpr (SMEM_BOX) {
-                // one batch of warp-uniform loads per step; the barrier keeps the compiler from hoisting them out
-                // of the loop, which would pin 2*D0 registers again
-                asm volatile("" ::: "memory");
-                if (PHILOX) {
-#pragma unroll
-                    for (int i = 0; i < D0; ++i) { lo[i] = s_lo[threadIdx.x >> 5][i]; range[i] = s_range[threadIdx.x >> 5][i]; }
-                }
-            }
-            fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
-                                          s1 - 1);
-            vis.commit(planes, active);
-        }
-#else
-        uint32_t cnt[(N + 3) / 4];
-#pragma unroll
-        for (int k = 0; k < (N + 3) / 4; ++k) cnt[k] = 0;
-        // one copy of the unrolled network: the ragged last step is handled by the per-sample activity flags
-        // (a second, flag-free copy for the full steps doubles the code and loses more in instruction fetch
-        // than the flags cost)
-        for (int sb = s0; sb < s1; sb += 32 * K) {
-            FbCountVisit<N, K> vis{cnt};
-#pragma unroll
-            for (int k = 0; k < K; ++k) vis.active[k] = (sb + 32 * k + lane) < s1;
-            if constexpr (SMEM_BOX) {
-                // one batch of warp-uniform loads per step; the barrier keeps the compiler from hoisting them out
-                // of the loop, which would pin 2*D0 registers again
-                asm volatile("" ::: "memory");
-                if (PHILOX) {
-#pragma unroll
-                    for (int i = 0; i < D0; ++i) { lo[i] = s_lo[threadIdx.x >> 5][i]; range[i] = s_range[threadIdx.x >> 5][i]; }
-                }
-            }
-            fb_profile_step<S, K, PHILOX>(prm, vis, lo, range, samples + (int64_t)p * nsamp * D0, sb + lane, pidx, seed,
-                                          s1 - 1);
-        }
-#endif
-        uint32_t mine = 0;
+        fb_profile_steps<S, K, PHILOX, G, SMEM_BOX>(prm, planes, lo, range, s_lo[SMEM_BOX ? threadIdx.x >> 5 : 0],
+                                                    s_range[SMEM_BOX ? threadIdx.x >> 5 : 0],
+                                                    samples + (int64_t)p * nsamp * D0, s0, s1, lane, pidx, seed);
+        uint32_t held = 0;
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-#if FB_PROFILE_BITSLICE
             uint32_t mycount = 0;
 #pragma unroll
             for (int b = 0; b < FB_PROFILE_PLANES; ++b) mycount |= ((planes[b][j >> 5] >> (j & 31)) & 1u) << b;
             const uint32_t tot = __reduce_add_sync(0xffffffffu, mycount);
-#else
-            const uint32_t tot = __reduce_add_sync(0xffffffffu, (cnt[j >> 2] >> (8 * (j & 3))) & 0xffu);
-#endif
-            if ((j & 31) == lane) mine = tot;
+            if ((j & 31) == lane) held = tot;
             if ((j & 31) == 31 || j == N - 1) {
                 const int jj = (j & ~31) + lane;
                 if (jj <= j) {
-                    if (chunks == 1) counts[p * N + jj] = mine;
-                    else atomicAdd(&counts[p * N + jj], mine);
+                    if (chunks == 1) counts[p * N + jj] = held;
+                    else atomicAdd(&counts[p * N + jj], held);
                 }
             }
         }
@@ -477,7 +453,7 @@ __device__ __forceinline__ void fb_spec_ibp(const SpecParams<S, double> &prm, co
                                             const double (&ub)[S::dim(l)], const double (&lbd)[S::dim(l)],
                                             const double (&ubd)[S::dim(l)], FbIbpSink<S> &sink)
 {
-    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), WO = S::woff(l), BO = S::boff(l);
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), BO = S::boff(l);
     constexpr bool last = (l == S::NL - 1);
     double nlb[OUT], nub[OUT], nlbd[OUT], nubd[OUT];
 #pragma unroll
@@ -485,7 +461,7 @@ __device__ __forceinline__ void fb_spec_ibp(const SpecParams<S, double> &prm, co
         double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
 #pragma unroll
         for (int i = 0; i < IN; ++i) {
-            const double w = prm.w[WO + i * OUT + j];
+            const double w = prm.w[S::widx(l, i, j)];
             const bool neg = fb_signbit(w);            // host canonicalises -0.0 to +0.0
             const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
             const double ad = neg ? ubd[i] : lbd[i], bd = neg ? lbd[i] : ubd[i];
@@ -631,6 +607,10 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
                 if (i == pa_col) { pa_lo = b.x; pa_hi = b.y; }
             }
         }
+        uint32_t widest = 0;
+#pragma unroll
+        for (int i = 0; i < D0; ++i) widest = max(widest, range[i]);
+        const int grp = fb_draw_group(widest);
         const int64_t pidx = first_index + p;
         unsigned long long best = ~0ull;
         for (int sb = s0; sb < s1; sb += 32) {
@@ -638,15 +618,9 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
             const bool active = s < s1;
             float x0[D0];
             if (PHILOX) {
-#pragma unroll
-                for (int blk = 0; blk * 4 < D0; ++blk) {
-                    uint32_t r[4];
-                    fb_philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
-                                     (uint32_t)seed, (uint32_t)(seed >> 32), r);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (blk * 4 + k < D0) x0[blk * 4 + k] = (float)fb_map_range(r[k], lo[blk * 4 + k], range[blk * 4 + k]);
-                }
+                if (grp == 4) fb_draw_spec<D0, 1, 4>(lo, range, s, pidx, seed, x0);
+                else if (grp == 2) fb_draw_spec<D0, 1, 2>(lo, range, s, pidx, seed, x0);
+                else fb_draw_spec<D0, 1, 1>(lo, range, s, pidx, seed, x0);
             } else {
                 const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
 #pragma unroll

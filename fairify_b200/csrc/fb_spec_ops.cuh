@@ -27,14 +27,14 @@ struct FbSpecOps {
     {
         P64 *p = new (std::nothrow) P64;
         if (!p) return nullptr;
-        std::memcpy(p->w, W, sizeof(p->w)); std::memcpy(p->b, B, sizeof(p->b));
+        fb_spec_fill(*p, W, B);
         return p;
     }
     static void *make_params32(const float *W, const float *B)
     {
         P32 *p = new (std::nothrow) P32;
         if (!p) return nullptr;
-        std::memcpy(p->w, W, sizeof(p->w)); std::memcpy(p->b, B, sizeof(p->b));
+        fb_spec_fill(*p, W, B);
         return p;
     }
     static void free_params(void *a, void *b) { delete static_cast<P64 *>(a); delete static_cast<P32 *>(b); }
@@ -44,15 +44,24 @@ struct FbSpecOps {
                                int num_sms, cudaStream_t st)
     {
         const P64 &prm = *static_cast<const P64 *>(p64);
-        const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
+        constexpr int WPC = FB_PROFILE_THREADS / 32;
+        const int64_t units = n * chunks;
+        // blocks of 32 units per warp once every resident warp gets several of them, single units otherwise
+        const int ublock = units >= (int64_t)64 * WPC * num_sms ? 32 : 1;
+        const int64_t ctas = ((units + ublock - 1) / ublock + WPC - 1) / WPC;
         if (philox) {
-            auto k = fb_profile_spec_kernel<S, true>;
-            k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts);
+            // one launch per draw class; each takes the partitions of its class (see the kernel)
+            auto k4 = fb_profile_spec_kernel<S, true, 4>;
+            auto k2 = fb_profile_spec_kernel<S, true, 2>;
+            auto k1 = fb_profile_spec_kernel<S, true, 1>;
+            const int grid = fb_grid_for(k4, FB_PROFILE_THREADS, 0, ctas, num_sms);
+            k4<<<grid, FB_PROFILE_THREADS, 0, st>>>(prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, ublock, counts);
+            k2<<<grid, FB_PROFILE_THREADS, 0, st>>>(prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, ublock, counts);
+            k1<<<grid, FB_PROFILE_THREADS, 0, st>>>(prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, ublock, counts);
         } else {
-            auto k = fb_profile_spec_kernel<S, false>;
+            auto k = fb_profile_spec_kernel<S, false, 1>;
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts);
+                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, ublock, counts);
         }
         return cudaGetLastError();
     }

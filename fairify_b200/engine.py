@@ -178,13 +178,17 @@ class Model:
         return t
 
     # -- the stage ------------------------------------------------------------------------------
-    def profile(self, boxes, S=1000, samples=None, seed=0, first_index=0):
-        """uint32-valued int32 tensor [n, N]: per neuron, the number of samples with a non-zero activation."""
+    def profile(self, boxes, S=1000, samples=None, seed=0, first_index=0, out=None):
+        """uint32-valued int32 tensor [n, N]: per neuron, the number of samples with a non-zero activation
+        (written into `out` when given: contiguous int32 [n, N] on this device)."""
         boxes = self._dev(boxes, torch.int32); n = boxes.shape[0]
         samples = self._dev(samples, torch.int32)
         if samples is not None:
             S = samples.shape[1]
-        counts = torch.empty((n, self.N), dtype=torch.int32, device=self.device)
+        counts = torch.empty((n, self.N), dtype=torch.int32, device=self.device) if out is None else out
+        if out is not None and (out.dtype != torch.int32 or tuple(out.shape) != (n, self.N) or not out.is_contiguous()
+                                or out.device != boxes.device):
+            raise ValueError("profile: out must be a contiguous int32 [n, N] tensor on the model's device")
         check(_lib.lib().fb_profile(self._h, n, _ptr(boxes), _ptr(samples), int(S), C.c_uint64(seed), int(first_index),
                                     _ptr(counts), _stream()), "fb_profile")
         return counts

@@ -14,8 +14,10 @@
  *             `model.layers[i].get_weights()` returns in the drivers (src/AC/Verify-AC.py:97-99)
  *   boxes     int32 [n][d][2] = (lo, hi) per feature in DataFrame COLUMN order
  *             (the order utils/prune.py:108-114 looks the range_dict up in)
- *   samples   int32 [n][S][d], or NULL to draw them on the device (Philox4x32-10, counter =
- *             (sample, partition index, feature/4), key = seed)
+ *   samples   int32 [n][S][d], or NULL to draw them on the device: Philox4x32-10, counter = (sample,
+ *             partition index, block), key = seed; each 32-bit word yields 4, 2 or 1 bounded integers (multiply-
+ *             shift, the low half of the product handed on) depending on whether the box's widest range is
+ *             <= 16, <= 256 or larger, so every value is uniform to within 2^-16 relative
  *   masks     uint32 [n][NW], NW = ceil(N/32); bit k = neuron k, neurons numbered layer by layer,
  *             output neuron included (N = sum of layer widths)
  *   per-neuron arrays  [n][N] in the same numbering
@@ -97,8 +99,10 @@ int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const uint32_t *c
 int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
              int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
 
-/* Same with HOST buffers in and out (boxes, samples, tol and every non-NULL output are host pointers;
- * pinned memory makes the copies asynchronous).  Copies in, runs, copies out, synchronises the stream. */
+/* Same with HOST buffers in and out (boxes, samples, tol and every non-NULL output are host pointers).
+ * The batch is processed in slices of 10^6 partitions through a three-stage pipeline -- upload, kernels (on
+ * `stream`), download -- on two internal copy streams, so with pinned host memory the copies hide behind the
+ * kernels; results do not depend on the slicing.  Returns after everything has finished. */
 int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
                   int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
 

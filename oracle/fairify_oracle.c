@@ -260,8 +260,8 @@ void fo_ibp_directed(int L, const int32_t *dims, const double *W, const double *
 
 /* ------------------------------------------------------------------------------------------------
  * Device-RNG restatement (throughput mode; the reference's MT19937 stream is injected from the host
- * in parity mode).  Philox4x32-10, counter = (sample, partition_lo, partition_hi, feature/4),
- * key = (seed_lo, seed_hi); word feature%4 is mapped to lo + mulhi(word, hi-lo+1).
+ * in parity mode).  Philox4x32-10, counter = (sample, partition_lo, partition_hi, block),
+ * key = (seed_lo, seed_hi); words are turned into bounded integers by fo_sample_row below.
  * Replaces utils/prune.py:205-222 (simluate_data: uniform integer in [lo, hi] per feature).
  * ---------------------------------------------------------------------------------------------- */
 static inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
@@ -277,17 +277,36 @@ static inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+/* Batched bounded integers: feature i takes the high half of word * range_i and hands the low half on as the
+ * word of the next feature of its group.  G features share one Philox word, G chosen from the box's widest range so
+ * that the product of the ranges drawn from one word stays <= 2^16: widest <= 16 -> 4, <= 256 -> 2, else 1.
+ * Word q of a sample is output q % 4 of the Philox block with counter (sample, partition_lo, partition_hi, q / 4). */
+static inline int fo_draw_group(int d, const int32_t *box)
+{
+    uint32_t widest = 0;
+    for (int i = 0; i < d; ++i) {
+        uint32_t range = (uint32_t)(box[2 * i + 1] - box[2 * i] + 1);
+        if (range > widest) widest = range;
+    }
+    return widest <= 16u ? 4 : (widest <= 256u ? 2 : 1);
+}
+
 static inline void fo_sample_row(uint64_t seed, int64_t pidx, int s, int d, const int32_t *box, int32_t *x)
 {
-    for (int blk = 0; blk * 4 < d; ++blk) {
-        uint32_t r[4];
-        philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)blk,
-                      (uint32_t)seed, (uint32_t)(seed >> 32), r);
-        for (int k = 0; k < 4 && blk * 4 + k < d; ++k) {
-            int i = blk * 4 + k;
-            uint32_t range = (uint32_t)(box[2 * i + 1] - box[2 * i] + 1);
-            x[i] = box[2 * i] + (int32_t)(((uint64_t)r[k] * range) >> 32);
+    const int G = fo_draw_group(d, box);
+    uint32_t r[4] = {0, 0, 0, 0}, word = 0;
+    for (int i = 0; i < d; ++i) {
+        if (i % G == 0) {
+            int q = i / G;
+            if (q % 4 == 0)
+                philox4x32_10((uint32_t)s, (uint32_t)pidx, (uint32_t)((uint64_t)pidx >> 32), (uint32_t)(q / 4),
+                              (uint32_t)seed, (uint32_t)(seed >> 32), r);
+            word = r[q % 4];
         }
+        uint32_t range = (uint32_t)(box[2 * i + 1] - box[2 * i] + 1);
+        uint64_t prod = (uint64_t)word * range;
+        x[i] = box[2 * i] + (int32_t)(uint32_t)(prod >> 32);
+        word = (uint32_t)prod;
     }
 }
 

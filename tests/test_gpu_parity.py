@@ -140,6 +140,54 @@ def test_profile_few_partitions_uses_sample_chunks(eng, name):
     assert np.array_equal(counts, counts2)
 
 
+def _mixed_class_boxes(d, n, seed):
+    """Synthetic boxes (not tied to a dataset's domain) whose widest range puts them, irregularly interleaved, in each
+    of the three draw classes: 4, 2 and 1 features per Philox word."""
+    rng = np.random.RandomState(seed)
+    cap = np.array([16, 256, 5000])[rng.randint(0, 3, size=n)]                 # class of each box
+    lo = rng.randint(-40, 60, size=(n, d))
+    width = 1 + (rng.rand(n, d) * cap[:, None]).astype(np.int64)
+    width[np.arange(n), rng.randint(0, d, size=n)] = cap                         # one feature at the class limit
+    return np.stack([lo, lo + width - 1], axis=2).astype(np.int32)
+
+
+@pytest.mark.parametrize("name", ["AC-1", "GC-1", "BM-1", "AC-7", "BM-4"])
+def test_profile_mixed_draw_classes(eng, name):
+    """one batch holding boxes of all three draw classes: every partition is handled exactly once, by the launch of
+    its own class, and matches the oracle's samples (specialised and runtime-shape kernels, partition screen too)."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    n, S = (61 if m.P > 4000 else 301), 70
+    hb = _mixed_class_boxes(m.d, n, 17)
+    widest = (hb[:, :, 1] - hb[:, :, 0] + 1).max(axis=1)
+    assert (widest <= 16).any() and ((widest > 16) & (widest <= 256)).any() and (widest > 256).any()
+    boxes = torch.as_tensor(hb).cuda()
+    samples = O.philox_samples(21, 1000, hb, S)
+    assert np.all(samples >= hb[:, None, :, 0]) and np.all(samples <= hb[:, None, :, 1])
+    counts = torch.full((n, m.N), -1, dtype=torch.int32, device="cuda")          # poisoned: every row must be written
+    counts = m.profile(boxes, S=S, seed=21, first_index=1000, out=counts).cpu().numpy()
+    assert np.array_equal(counts.astype(np.uint32), O.profile(net, samples))
+    pa_col = dom.columns.index(dom.pa[0])
+    ce = m.partition_screen(boxes, pa_col, S=S, seed=21, first_index=1000)[0].cpu().numpy()
+    assert np.array_equal(ce, O.partition_screen(net, samples, hb, pa_col)[0])
+
+
+def test_profile_block_scheduling_large_batch(eng):
+    """enough partitions for the 32-units-per-warp scheduling, mixed classes, ragged tail: counts against the oracle."""
+    w, b = G.wb("AC-1")
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain("AC-1")
+    n, S = 160_003, 40
+    hb = _mixed_class_boxes(m.d, n, 23)
+    hb[: n // 2, :, 1] = np.minimum(hb[: n // 2, :, 1], hb[: n // 2, :, 0] + 3)   # first half: one class only, second half mixed
+    boxes = torch.as_tensor(hb).cuda()
+    counts = torch.full((n, m.N), -1, dtype=torch.int32, device="cuda")
+    counts = m.profile(boxes, S=S, seed=8, first_index=5, out=counts).cpu().numpy()
+    want = O.profile(net, O.philox_samples(8, 5, hb, S))
+    assert np.array_equal(counts.astype(np.uint32), want)
+
+
 @pytest.mark.parametrize("name", ["AC-1", "AC-12", "GC-2", "BM-1"])
 def test_generic_kernels_agree_with_specialised(eng, name):
     """FAIRIFY_B200_FORCE_GENERIC routes a specialised shape through the runtime-shape kernels (subprocess)."""

@@ -144,6 +144,61 @@ def test_philox_samples_in_range_and_uniform():
         assert cnt.min() > 0.7 * 4000 / len(vals)
 
 
+def _philox_py(c, k):
+    c = list(c); k = list(k); M = 0xFFFFFFFF
+    for _ in range(10):
+        p0 = 0xD2511F53 * c[0]; p1 = 0xCD9E8D57 * c[2]
+        c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & M, (p0 >> 32) ^ c[3] ^ k[1], p0 & M]
+        k = [(k[0] + 0x9E3779B9) & M, (k[1] + 0xBB67AE85) & M]
+    return c
+
+
+def _draw_py(seed, pidx, s, box):
+    """Pure-Python restatement of the batched bounded-integer draw (fb_common.cuh / fo_sample_row)."""
+    widest = max(int(hi) - int(lo) + 1 for lo, hi in box)
+    G = 4 if widest <= 16 else (2 if widest <= 256 else 1)
+    out = []; word = 0; r = None
+    for i, (lo, hi) in enumerate(box):
+        if i % G == 0:
+            q = i // G
+            if q % 4 == 0:
+                r = _philox_py([s, pidx & 0xFFFFFFFF, pidx >> 32, q // 4], [seed & 0xFFFFFFFF, seed >> 32])
+            word = r[q % 4]
+        prod = word * (int(hi) - int(lo) + 1)
+        out.append(int(lo) + (prod >> 32)); word = prod & 0xFFFFFFFF
+    return out
+
+
+@pytest.mark.parametrize("widths", [[4, 3, 1, 2, 4, 4, 2, 16, 5, 1, 3, 2, 4], [100, 7, 2, 256, 30, 1, 9, 64, 3],
+                                    [100, 20001, 5, 2, 80, 3], [10] * 20])
+def test_batched_draw_matches_python_restatement(widths):
+    """All three draw classes (4, 2, 1 features per Philox word) against an independent pure-Python restatement."""
+    rng = np.random.RandomState(5)
+    lo = rng.randint(-50, 50, size=len(widths))
+    boxes = np.stack([lo, lo + np.array(widths) - 1], axis=1).astype(np.int32)[None]
+    got = O.philox_samples(0x1234567890ABCDEF, (1 << 33) + 11, boxes, 40)[0]
+    for s in range(40):
+        assert got[s].tolist() == _draw_py(0x1234567890ABCDEF, (1 << 33) + 11, s, boxes[0])
+
+
+@pytest.mark.parametrize("widths", [[4, 3, 16, 2, 5, 4, 4, 4, 7], [100, 7, 256, 2, 30, 30]])
+def test_batched_draw_is_uniform_and_independent(widths):
+    """Values drawn from one shared Philox word are uniform and pairwise independent (chi-square, 6 sigma)."""
+    S = 200000
+    boxes = np.stack([np.zeros(len(widths)), np.array(widths) - 1], axis=1).astype(np.int32)[None]
+    s = O.philox_samples(99, 3, boxes, S)[0]
+    for i, w in enumerate(widths):
+        cnt = np.bincount(s[:, i], minlength=w)
+        chi2 = ((cnt - S / w) ** 2 / (S / w)).sum()
+        assert chi2 < (w - 1) + 6 * np.sqrt(2 * max(w - 1, 1)), (i, chi2)
+    for i in range(len(widths) - 1):                    # neighbours (share a word whenever they are in one group)
+        wa, wb = widths[i], widths[i + 1]
+        joint = np.bincount(s[:, i] * wb + s[:, i + 1], minlength=wa * wb)
+        dof = wa * wb - 1
+        chi2 = ((joint - S / (wa * wb)) ** 2 / (S / (wa * wb))).sum()
+        assert chi2 < dof + 6 * np.sqrt(2 * dof), (i, chi2)
+
+
 @pytest.mark.parametrize("tag", ["AC_T30", "AC_T12"])
 def test_point_to_partition_density(tag):
     """p_list_density (utils/input_partition.py:184-218): rows per partition via index arithmetic == the reference's scan."""

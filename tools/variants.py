@@ -2,7 +2,7 @@
 """Build tuning variants of the specialised AC kernels (only fb_spec_a.cu is recompiled) and, on a GPU box,
 time fb_profile for each.  Development aid, not part of the product.
 
-    python tools/variants.py build  tag:-DFB_PROFILE_SPT=3 tag2:"-DFB_PROFILE_IM=0 -DFB_PROFILE_MINB=3" ...
+    python tools/variants.py build  tag:-DFB_PROFILE_SPT=3 tag2:"-DFB_SPEC_JB=2 -DFB_PROFILE_MINB=2" ...
     python tools/variants.py run    tag tag2 ...          (on the GPU box)
 """
 import concurrent.futures as cf, glob, os, subprocess, sys
@@ -28,7 +28,7 @@ def build(specs):
         subprocess.check_call([B._nvcc(), "-shared", "-o", so, obj] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ccbin", "/usr/bin/g++"])
         import re
         txt = open(log).read()
-        m = re.search(r"fb_profile_spec_kernelI4SpecIJLi13ELi16ELi8ELi1EEELb1.*?\n.*?\n\s*(\d+) bytes stack frame, (\d+) bytes spill stores.*?\n.*?Used (\d+) registers", txt, re.S)
+        m = re.search(r"fb_profile_spec_kernelI4SpecIJLi13ELi16ELi8ELi1EEELb1ELi4E.*?\n.*?\n\s*(\d+) bytes stack frame, (\d+) bytes spill stores.*?\n.*?Used (\d+) registers", txt, re.S)
         return tag, (m.groups() if m else None)
     with cf.ThreadPoolExecutor(max_workers=8) as ex:
         for tag, info in ex.map(one, specs):
