@@ -1,5 +1,7 @@
 // fb_api.cu -- C ABI of libfairify_b200.so (declared in include/fairify_b200.h) and the runtime-shape
 // kernel launchers.  No torch types; device pointers, sizes and a cudaStream_t (as void*) only.
+#include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -63,6 +65,36 @@ struct fb_model {
     const FbSpecEntry *spec = nullptr;
     void *p64 = nullptr, *p32 = nullptr;
 };
+
+// The specialised profile kernel tests "pre-activation > 0" on the high word of the double, which misreads positive
+// subnormals below 2^-1042.  They cannot occur when every hidden pre-activation is a multiple of some 2^q with
+// q >= -1022: sample features are integers, so layer 0's pre-activations are multiples of 2^q0, q0 = the smallest
+// exponent of a least-significant set bit among W0 and b0; a layer's products are multiples of 2^(q_prev + its
+// weights' smallest such exponent), and rounding a multiple of 2^q to nearest gives a multiple of 2^q again.  A non-zero
+// multiple of 2^q with q >= -1022 is a normal number.  Keras float32 weights give q >= -149 per layer, so only
+// pathological models (subnormal weights through many layers) fail this and take the runtime-shape kernels.
+static int fb_lsb_exponent(double v)
+{
+    if (v == 0.0) return INT32_MAX;
+    int e;
+    const double m = std::frexp(std::fabs(v), &e);                 // v = m * 2^e, 0.5 <= m < 1
+    const uint64_t M = (uint64_t)std::ldexp(m, 53);                // 53-bit integer mantissa
+    return e - 53 + __builtin_ctzll(M);
+}
+static bool fb_model_subnormal_free(const GenNet &g, const std::vector<double> &W, const std::vector<double> &B)
+{
+    int64_t q = 0;                                                 // inputs are integers
+    for (int l = 0; l + 1 < g.L; ++l) {                            // hidden layers only: the logit uses the full test
+        int wmin = INT32_MAX, bmin = INT32_MAX;
+        for (int k = g.woff[l]; k < g.woff[l + 1]; ++k) wmin = std::min(wmin, fb_lsb_exponent(W[k]));
+        for (int k = g.boff[l]; k < g.boff[l + 1]; ++k) bmin = std::min(bmin, fb_lsb_exponent(B[k]));
+        const int64_t prod = (wmin == INT32_MAX) ? INT32_MAX : q + wmin;
+        q = std::min<int64_t>(prod, bmin);
+        if (q == INT32_MAX) q = 0;                                 // an all-zero layer: everything after it restarts from the biases
+        if (q < -1022) return false;
+    }
+    return true;
+}
 
 static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
 {
@@ -134,6 +166,7 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
     }
     g.W64 = m->dW64; g.B64 = m->dB64; g.W32 = m->dW32; g.B32 = m->dB32;
     m->spec = fb_find_spec(L, dims);
+    if (m->spec && !fb_model_subnormal_free(g, m->hW64, m->hB64)) m->spec = nullptr;   // runtime-shape kernels: exact sign test
     if (m->spec) {
         m->p64 = m->spec->make_params64(m->hW64.data(), m->hB64.data());
         m->p32 = m->spec->make_params32(m->hW32.data(), m->hB32.data());
@@ -486,8 +519,13 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
     FB_CUDA(cudaStreamWaitEvent(up, ready, 0));
     FB_CUDA(cudaStreamWaitEvent(down, ready, 0));
     int rc = FB_OK;
-    for (int64_t off = 0; off < n && rc == FB_OK; off += FB_HOST_SLICE) {
-        const int64_t cnt = std::min<int64_t>(FB_HOST_SLICE, n - off);
+    static const int64_t slice = [] {                    // FAIRIFY_B200_HOST_SLICE overrides the slice size (tuning aid)
+        const char *v = getenv("FAIRIFY_B200_HOST_SLICE");
+        const long long x = v ? atoll(v) : 0;
+        return x > 0 ? (int64_t)x : (int64_t)FB_HOST_SLICE;
+    }();
+    for (int64_t off = 0; off < n && rc == FB_OK; off += slice) {
+        const int64_t cnt = std::min<int64_t>(slice, n - off);
         cudaEvent_t uploaded, computed;
         FB_CUDA(events.make(&uploaded));
         FB_CUDA(events.make(&computed));

@@ -159,6 +159,10 @@ struct GenNet {
 // small arithmetic helpers
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool fb_pos(double v) { return __double_as_longlong(v) > 0; }   // v > 0 (no NaNs here)
+// v > 0 from the high word alone: exact unless v is a positive subnormal below 2^-1042.  Only used by the specialised
+// profile kernel, which fb_model_create selects only for models that cannot produce a subnormal pre-activation
+// (fb_model_subnormal_free in fb_api.cu).
+__device__ __forceinline__ bool fb_pos_hi(double v) { return __double2hiint(v) > 0; }
 __device__ __forceinline__ bool fb_pos(float v) { return __float_as_int(v) > 0; }
 __device__ __forceinline__ bool fb_nonzero(double v) { return (__double_as_longlong(v) << 1) != 0; }
 __device__ __forceinline__ bool fb_signbit(double v) { return __double2hiint(v) < 0; }

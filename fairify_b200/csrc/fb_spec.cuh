@@ -116,7 +116,9 @@ struct FbMaskedVisit {
 
 #define FB_PROFILE_PLANES 7          // bit-sliced counters count to 127 per lane
 
-template <int N, int K>
+// HI_SIGN: hidden neurons' "pre-activation > 0" read from the high word (fb_pos_hi; needs the subnormal-free guarantee
+// fb_model_create establishes for every model it gives to these kernels)
+template <int N, int K, bool HI_SIGN>
 struct FbCountVisit {
     // One bit per neuron and sample: neuron idx sets bit idx of nzmask[k].  After the forward pass the masks
     // are added into `planes`, a bit-sliced counter (planes[b] holds bit b of every neuron's count): two
@@ -136,7 +138,7 @@ struct FbCountVisit {
         VecD<K> r;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            const bool pos = fb_pos(pre.v[k]);
+            const bool pos = HI_SIGN ? fb_pos_hi(pre.v[k]) : fb_pos(pre.v[k]);
             const bool nz = last ? fb_nonzero(pre.v[k]) : pos;
             if (nz) nzmask[k][idx >> 5] |= 1u << (idx & 31);
             r.v[k] = last ? pre.v[k] : (pos ? pre.v[k] : 0.0);
@@ -234,6 +236,15 @@ __host__ __device__ constexpr bool fb_profile_smem_box()
     return FB_PROFILE_SMEM_BOX && S::N <= 64;
 }
 
+// The one-instruction sign test pays for the small shapes; on the 100-wide and the deep funnel shapes it changes
+// ptxas' schedule for the worse (more weights hoisted into uniform registers and spilled: AC-2 63 -> 59 %, AC-7
+// 48 -> 43 % of FP64 peak on B200), so those keep the full compare.
+template <class S>
+__host__ __device__ constexpr bool fb_profile_hi_sign()
+{
+    return fb_profile_smem_box<S>();
+}
+
 // all steps of one (partition, sample chunk): samples [s0, s1), 32*K per step, counted into the bit-sliced planes
 template <class S, int K, bool PHILOX, int G, bool SMEM_BOX>
 __device__ __forceinline__ void fb_profile_steps(const SpecParams<S, double> &prm,
@@ -244,7 +255,7 @@ __device__ __forceinline__ void fb_profile_steps(const SpecParams<S, double> &pr
                                                  uint64_t seed)
 {
     for (int sb = s0; sb < s1; sb += 32 * K) {
-        FbCountVisit<S::N, K> vis;
+        FbCountVisit<S::N, K, fb_profile_hi_sign<S>()> vis;
         vis.begin();
         bool active[K];
 #pragma unroll
@@ -268,7 +279,7 @@ __device__ __forceinline__ void fb_profile_steps(const SpecParams<S, double> &pr
 //
 // With PHILOX the kernel exists once per draw class G and a launch handles exactly the partitions whose box has that
 // class (the launcher runs G = 4, 2, 1 one after the other; every partition is taken by one of them).  Work is handed
-// out in blocks of `ublock` (1 or 32) consecutive units: lane t classifies unit t of the block, so skipping a block
+// out in blocks of `ublock` (1 ... 32) consecutive units: lane t classifies unit t of the block, so skipping a block
 // that belongs to another launch costs one round of loads per 32 partitions.
 template <class S, bool PHILOX, int G>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS, FB_PROFILE_MINB)
@@ -305,8 +316,9 @@ fb_profile_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_
         // in shared memory (one copy per warp) and is re-read at the top of every step, instead of holding 2*D0
         // registers through the network; SMEM_BOX is false for the shapes where that measured slower.
         constexpr bool SMEM_BOX = fb_profile_smem_box<S>();
-        __shared__ int32_t s_lo[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0 : 1];
-        __shared__ uint32_t s_range[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0 : 1];
+        constexpr int D0P = (D0 + 3) & ~3;               // rows padded to 16 bytes: read back as 128-bit words
+        __shared__ __align__(16) int32_t s_lo[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0P : 4];
+        __shared__ __align__(16) uint32_t s_range[SMEM_BOX ? FB_PROFILE_THREADS / 32 : 1][SMEM_BOX ? D0P : 4];
         int32_t lo[D0];
         uint32_t range[D0];
         if (PHILOX) {

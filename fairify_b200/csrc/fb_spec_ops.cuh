@@ -1,6 +1,7 @@
 // fb_spec_ops.cuh -- host launchers for one Spec<...>; included by the fb_spec_*.cu instantiation units.
 #pragma once
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -46,8 +47,14 @@ struct FbSpecOps {
         const P64 &prm = *static_cast<const P64 *>(p64);
         constexpr int WPC = FB_PROFILE_THREADS / 32;
         const int64_t units = n * chunks;
-        // blocks of 32 units per warp once every resident warp gets several of them, single units otherwise
-        const int ublock = units >= (int64_t)64 * WPC * num_sms ? 32 : 1;
+        // Units are handed to warps in blocks of `ublock` (a launch's last round leaves some warps one block short:
+        // keep that under ~1/64 of a warp's work), 32 at most -- the lanes of a warp classify one unit each
+        int ublock = 1;
+        while (ublock < 32 && units >= (int64_t)64 * (2 * ublock) * WPC * num_sms) ublock *= 2;
+        if (const char *v = getenv("FAIRIFY_B200_UBLOCK")) {          // test hook: force the block size (1 ... 32)
+            const int x = atoi(v);
+            if (x >= 1 && x <= 32) ublock = x;
+        }
         const int64_t ctas = ((units + ublock - 1) / ublock + WPC - 1) / WPC;
         if (philox) {
             // one launch per draw class; each takes the partitions of its class (see the kernel)

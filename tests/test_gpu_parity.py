@@ -173,12 +173,18 @@ def test_profile_mixed_draw_classes(eng, name):
     assert np.array_equal(ce, O.partition_screen(net, samples, hb, pa_col)[0])
 
 
-def test_profile_block_scheduling_large_batch(eng):
-    """enough partitions for the 32-units-per-warp scheduling, mixed classes, ragged tail: counts against the oracle."""
+@pytest.mark.parametrize("ublock", ["32", "5", None])
+def test_profile_block_scheduling_large_batch(eng, ublock, monkeypatch):
+    """work handed out in blocks of consecutive partitions (forced to 32 and to an odd size through the test hook, then
+    the launcher's own choice), mixed classes, ragged tail: counts against the oracle."""
+    if ublock is None:
+        monkeypatch.delenv("FAIRIFY_B200_UBLOCK", raising=False)
+    else:
+        monkeypatch.setenv("FAIRIFY_B200_UBLOCK", ublock)
     w, b = G.wb("AC-1")
     m = eng.Model(w, b); net = O.Net(w, b)
     dom = G.domain("AC-1")
-    n, S = 160_003, 40
+    n, S = 40_003, 40
     hb = _mixed_class_boxes(m.d, n, 23)
     hb[: n // 2, :, 1] = np.minimum(hb[: n // 2, :, 1], hb[: n // 2, :, 0] + 3)   # first half: one class only, second half mixed
     boxes = torch.as_tensor(hb).cuda()
@@ -186,6 +192,28 @@ def test_profile_block_scheduling_large_batch(eng):
     counts = m.profile(boxes, S=S, seed=8, first_index=5, out=counts).cpu().numpy()
     want = O.profile(net, O.philox_samples(8, 5, hb, S))
     assert np.array_equal(counts.astype(np.uint32), want)
+
+
+def test_subnormal_capable_model_takes_exact_sign_test(eng):
+    """The specialised profile kernel reads a pre-activation's sign from its high word, which is only exact when no
+    positive subnormal can occur; a 10-layer net of subnormal float32 weights could produce them, so it must be routed
+    to the runtime-shape kernels -- and still match the oracle, whose compare is exact."""
+    dims = [13, 5, 5, 5, 5, 5, 5, 5, 5, 5, 1]
+    rng = np.random.RandomState(3)
+    tiny = np.float32(2.0 ** -136)             # the last hidden layer's pre-activations land near 2^-1056
+    w = [(rng.randint(1, 4, size=(a, b)).astype(np.float32) * (np.float32(1.0) if l == 0 else tiny))
+         for l, (a, b) in enumerate(zip(dims[:-1], dims[1:]))]
+    b = [np.zeros(n, dtype=np.float32) for n in dims[1:]]
+    m = eng.Model(w, b); net = O.Net(w, b)
+    assert not m.specialised
+    ok = eng.Model(*G.wb("AC-12"))
+    assert ok.specialised                      # the real AC-12 (same shape) keeps the specialised kernels
+    dom = G.domain("AC-12")
+    boxes = eng.Grid(dom.columns, dom.ranges, dom.threshold).boxes(0, 50)
+    counts = m.profile(boxes, S=64, seed=4).cpu().numpy()
+    want = O.profile(net, O.philox_samples(4, 0, boxes.cpu().numpy(), 64))
+    assert np.array_equal(counts.astype(np.uint32), want)
+    assert want[:, 40:45].all()                # the last hidden layer is active with values below 2^-1042
 
 
 @pytest.mark.parametrize("name", ["AC-1", "AC-12", "GC-2", "BM-1"])
