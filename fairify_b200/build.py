@@ -48,9 +48,12 @@ def build(force=False, verbose=False):
     sources = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     nvcc = _nvcc()
     jobs = []
+    # the specialisation units include neither the runtime-shape kernels nor the public header
+    spec_headers = [h for h in headers if os.path.basename(h) not in ("fb_generic.cuh", "fairify_b200.h")]
     for src in sources:
         obj = os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
-        if force or _stale(obj, [src] + headers):
+        deps = spec_headers if os.path.basename(src).startswith("fb_spec_") else headers
+        if force or _stale(obj, [src] + deps):
             jobs.append((src, obj))
 
     def compile_one(job):

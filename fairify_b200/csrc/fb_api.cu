@@ -64,6 +64,8 @@ struct fb_model {
     float *dW32 = nullptr, *dB32 = nullptr;
     const FbSpecEntry *spec = nullptr;
     void *p64 = nullptr, *p32 = nullptr;
+    FbTileNet tile{};               // padded float64 weights for the tiled profile kernel
+    double *dWpad = nullptr;
 };
 
 // The specialised profile kernel tests "pre-activation > 0" on the high word of the double, which misreads positive
@@ -115,7 +117,7 @@ extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad);
     delete m;
 }
 
@@ -165,6 +167,24 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         return fb_fail(FB_ERR_CUDA, "fb_model_create: %s (is a CUDA device available? there is no CPU path)", cudaGetErrorString(e));
     }
     g.W64 = m->dW64; g.B64 = m->dB64; g.W32 = m->dW32; g.B32 = m->dB32;
+    {
+        // weights with every row padded to a multiple of 32 columns (zeros): operand of fb_profile_tile_kernel
+        FbTileNet &t = m->tile;
+        t.L = L; t.N = g.N; t.maxw = g.maxw;
+        int off = 0;
+        for (int l = 0; l <= L; ++l) { t.dims[l] = g.dims[l]; t.dimsp[l] = (g.dims[l] + 31) & ~31; t.boff[l] = g.boff[l]; }
+        for (int l = 0; l < L; ++l) { t.woffp[l] = off; off += g.dims[l] * t.dimsp[l + 1]; }
+        t.woffp[L] = off;
+        std::vector<double> wp((size_t)off, 0.0);
+        for (int l = 0; l < L; ++l)
+            for (int i = 0; i < g.dims[l]; ++i)
+                for (int j = 0; j < g.dims[l + 1]; ++j)
+                    wp[(size_t)t.woffp[l] + (size_t)i * t.dimsp[l + 1] + j] = m->hW64[(size_t)g.woff[l] + (size_t)i * g.dims[l + 1] + j];
+        e = cudaMalloc(&m->dWpad, sizeof(double) * wp.size());
+        if (e == cudaSuccess) e = cudaMemcpy(m->dWpad, wp.data(), sizeof(double) * wp.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
+        t.Wp = m->dWpad; t.B = m->dB64;
+    }
     m->spec = fb_find_spec(L, dims);
     if (m->spec && !fb_model_subnormal_free(g, m->hW64, m->hB64)) m->spec = nullptr;   // runtime-shape kernels: exact sign test
     if (m->spec) {
@@ -353,6 +373,48 @@ static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const vo
     return FB_OK;
 }
 
+// Runtime-shape profile: the tiled kernel (fb_generic.cuh) for the big networks, the sample-per-lane kernel for the
+// rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane): BM-4 27 vs 11, AC-4 25 vs 13, AC-5 / BM-7 30 vs
+// 20, but GC-5 (a funnel of mostly narrow layers, 4004 weights) 19 vs 21 -- hence the weight-count threshold.
+// FAIRIFY_B200_TILED_PROFILE=1 / 0 forces one or the other (tests, comparisons).
+static bool fb_use_tiled_profile(const fb_model *m)
+{
+    static const int forced = [] { const char *v = getenv("FAIRIFY_B200_TILED_PROFILE"); return !v ? -1 : (v[0] == '0' ? 0 : 1); }();
+    if (forced >= 0) return forced == 1;
+    return m->gen.P >= 4500;
+}
+
+template <int TM>
+static int fb_profile_tiled_launch(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                   uint64_t seed, int64_t first_index, uint32_t *counts, cudaStream_t st)
+{
+    const size_t smem = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, TM);
+    const int64_t units = n * ((S + TM - 1) / TM);
+    if (samples == nullptr) {
+        auto k = fb_profile_tile_kernel<TM, true>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_TILE_THREADS, smem, units, m->num_sms), FB_TILE_THREADS, smem, st>>>(
+            m->tile, n, boxes, samples, seed, first_index, S, counts);
+    } else {
+        auto k = fb_profile_tile_kernel<TM, false>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_TILE_THREADS, smem, units, m->num_sms), FB_TILE_THREADS, smem, st>>>(
+            m->tile, n, boxes, samples, seed, first_index, S, counts);
+    }
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+static int fb_profile_tiled(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                            int64_t first_index, uint32_t *counts, bool already_zeroed, cudaStream_t st)
+{
+    if (!already_zeroed) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));   // the kernel adds
+    // 128 samples per CTA when the activation buffers of that height fit beside the weight stages, else 64
+    const size_t smem128 = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, 128);
+    if (smem128 <= 220 * 1024) return fb_profile_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
+}
+
 static size_t fb_profile_gen_smem(const fb_model *m)
 {
     return sizeof(double) * ((size_t)m->gen.P + m->gen.N) + sizeof(uint32_t) * (FB_PROFILE_THREADS / 32) * m->gen.N;
@@ -373,6 +435,7 @@ extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, co
                                  counts, m->num_sms, st));
         return FB_OK;
     }
+    if (fb_use_tiled_profile(m)) return fb_profile_tiled(m, n, boxes, samples, S, seed, first_index, counts, chunks > 1, st);
     const size_t smem = fb_profile_gen_smem(m);
     if (smem > 227 * 1024) return fb_fail(FB_ERR_UNSUPPORTED, "fb_profile: model needs %zu bytes of shared memory", smem);
     const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);

@@ -73,7 +73,7 @@ __device__ __forceinline__ int32_t fb_draw_next(uint32_t &word, int32_t lo, uint
 // OUT is double or float.
 template <typename OUT>
 __device__ __forceinline__ void fb_draw_row(const int32_t *__restrict__ box, int D0, int G, uint32_t s, int64_t pidx,
-                                            uint64_t seed, OUT *x)
+                                            uint64_t seed, OUT *x, int stride = 1)
 {
     const int nwords = (D0 + G - 1) / G;
     for (int blk = 0; blk * 4 < nwords; ++blk) {
@@ -88,7 +88,7 @@ __device__ __forceinline__ void fb_draw_row(const int32_t *__restrict__ box, int
                 const int i = (blk * 4 + k) * G + g;
                 if (g < G && i < D0) {
                     const int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
-                    x[i] = (OUT)fb_draw_next(word, lo, (uint32_t)(hi - lo + 1));
+                    x[(int64_t)i * stride] = (OUT)fb_draw_next(word, lo, (uint32_t)(hi - lo + 1));
                 }
             }
         }

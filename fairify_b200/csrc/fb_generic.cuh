@@ -74,6 +74,202 @@ struct FbGenCountVisit {
     }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// Activation profile for wide runtime-shape networks, organised like a tiled matrix product.
+//
+// A CTA takes TM samples of one partition through the whole network.  A layer is  C[m][n] = sum_k A[m][k] W[k][n]
+// with the samples as rows: the activations of the TM samples sit in shared memory ([k][m], two buffers that swap
+// roles from layer to layer), a warp owns a 32-sample x 32-neuron block of C, and a thread an (4 samples) x (8
+// neurons) register tile whose 32 accumulators each run  acc = fma(w, x, acc)  over k ascending -- per neuron exactly
+// the chain of the oracle and of the other kernels, so the counts are bit-identical.  Per k a thread loads 4
+// activations (shared memory, the 4 lanes that share the samples read the same words) and 8 weights (shared memory
+// too: the layer's rows, padded to 32 columns, stream through two cp.async stages of 16 rows) for 32 multiply-adds,
+// against one activation load per multiply-add of the sample-per-lane kernel below.
+// counts[p][N] is atomically added to (caller zeroes first).
+// ---------------------------------------------------------------------------------------------------
+struct FbTileNet {
+    int L, N;
+    int dims[FB_MAX_LAYERS + 1];     // true widths
+    int dimsp[FB_MAX_LAYERS + 1];    // widths rounded up to 32 (row pitch of the padded weights)
+    int woffp[FB_MAX_LAYERS + 1];    // layer offsets into Wp
+    int boff[FB_MAX_LAYERS + 1];
+    int maxw;                        // widest layer (inputs included): pitch of the activation buffers is TM
+    const double *Wp;                // [in][dimsp[l+1]] per layer, zero padded
+    const double *B;
+};
+
+#define FB_TILE_THREADS 256
+#define FB_TILE_KC 16            // weight rows per shared-memory stage
+
+__device__ __forceinline__ void fb_cp_async16(void *smem_dst, const void *gsrc)
+{
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void fb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void fb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// dynamic shared memory: two activation buffers [maxw][TM], two weight stages [KC][maxwp], per-neuron counters [N]
+__host__ __device__ inline size_t fb_tile_smem_bytes(int maxw, int maxwp, int N, int TM)
+{
+    return sizeof(double) * (2 * (size_t)maxw * TM + 2 * (size_t)FB_TILE_KC * maxwp) + sizeof(uint32_t) * N;
+}
+
+template <int TM, bool PHILOX>
+__global__ void __launch_bounds__(FB_TILE_THREADS)
+fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict__ boxes,
+                       const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp,
+                       uint32_t *__restrict__ counts)
+{
+    extern __shared__ __align__(16) unsigned char fb_smem[];
+    constexpr int KC = FB_TILE_KC;
+    double *buf0 = reinterpret_cast<double *>(fb_smem);               // activations: two [maxw][TM] buffers
+    const int bufsz = net.maxw * TM;
+    const int maxwp = (net.maxw + 31) & ~31;
+    double *wst = buf0 + 2 * (size_t)bufsz;                            // weights: two [KC][maxwp] stages
+    uint32_t *scnt = reinterpret_cast<uint32_t *>(wst + 2 * (size_t)KC * maxwp);
+    constexpr int MB = TM / 32;                           // 32-sample blocks of the tile
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lane_m = lane & 7, lane_n = lane >> 3;      // a warp's block: 8 lanes x 4 samples by 4 lanes x 8 neurons
+    const int D0 = net.dims[0], N = net.N;
+    const int tiles = (nsamp + TM - 1) / TM;
+    const int64_t units = n * tiles;
+    for (int k = tid; k < N; k += FB_TILE_THREADS) scnt[k] = 0;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+        const int64_t p = u / tiles;
+        const int s0 = (int)(u - p * tiles) * TM;
+        const int live = min(TM, nsamp - s0);             // samples of this tile that exist
+        // -- this tile's samples, feature-major: buf0[i * TM + m]
+        if (tid < TM) {
+            double *col = buf0 + tid;
+            if (tid < live) {
+                if (PHILOX) {
+                    const int32_t *box = boxes + p * (2 * D0);
+                    fb_draw_row<double>(box, D0, fb_draw_group(fb_box_widest(box, D0)), (uint32_t)(s0 + tid),
+                                        first_index + p, seed, col, TM);
+                } else {
+                    const int32_t *row = samples + ((int64_t)p * nsamp + s0 + tid) * D0;
+                    for (int i = 0; i < D0; ++i) col[(int64_t)i * TM] = (double)__ldg(row + i);
+                }
+            } else {
+                for (int i = 0; i < D0; ++i) col[(int64_t)i * TM] = 0.0;
+            }
+        }
+        __syncthreads();
+        for (int l = 0; l < net.L; ++l) {
+            const int IN = net.dims[l], OUT = net.dims[l + 1], OUTP = net.dimsp[l + 1];
+            const bool last = (l == net.L - 1);
+            const double *Ain = buf0 + (l & 1) * bufsz;
+            double *Aout = buf0 + ((l + 1) & 1) * bufsz;
+            const int nblocks = MB * (OUTP / 32);
+            const int nchunks = (IN + KC - 1) / KC;
+            const double *Wl = net.Wp + net.woffp[l];
+            if (OUT <= 8) {
+                // narrow layer (the logit, the tail of a funnel): a 32-column block would be mostly padding, so every
+                // thread takes whole dot products instead -- (sample, neuron) pairs, a warp's 32 pairs share the neuron
+                for (int t = tid; t < TM * OUT; t += FB_TILE_THREADS) {
+                    const int mm = t % TM, nn = t / TM;
+                    const double *ap = Ain + mm;
+                    const double *wp = Wl + nn;
+                    double acc = 0.0;
+#pragma unroll 4
+                    for (int k = 0; k < IN; ++k) acc = __fma_rn(__ldg(wp + (size_t)k * OUTP), ap[(size_t)k * TM], acc);
+                    const double pre = __dadd_rn(acc, __ldg(net.B + net.boff[l] + nn));
+                    const bool pos = fb_pos(pre);
+                    const bool nz = (last ? fb_nonzero(pre) : pos) && (mm < live);
+                    const uint32_t bal = __ballot_sync(0xffffffffu, nz);
+                    if (lane == 0 && bal) atomicAdd(&scnt[net.boff[l] + nn], (uint32_t)__popc(bal));
+                    if (!last) Aout[(size_t)nn * TM + mm] = pos ? pre : 0.0;
+                }
+                __syncthreads();
+                continue;
+            }
+            // the layer's weights stream through shared memory KC rows at a time (cp.async, two stages), all columns
+            auto stage = [&](int c) {
+                const int rows = min(KC, IN - c * KC);
+                const double2 *src = reinterpret_cast<const double2 *>(Wl + (size_t)c * KC * OUTP);
+                double2 *dst = reinterpret_cast<double2 *>(wst + (size_t)(c & 1) * KC * maxwp);
+                for (int i = tid; i < rows * (OUTP / 2); i += FB_TILE_THREADS) fb_cp_async16(dst + i, src + i);
+                fb_cp_async_commit();
+            };
+            for (int blk0 = 0; blk0 < nblocks; blk0 += FB_TILE_THREADS / 32) {       // rounds: one block per warp
+                const int blk = blk0 + warp;
+                const bool active = blk < nblocks;
+                const int mb = blk % MB, nb = blk / MB;
+                const int m0 = mb * 32 + lane_m * 4, n0 = nb * 32 + lane_n * 8;
+                double acc[4][8];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[r][j] = 0.0;
+                stage(0);
+                for (int c = 0; c < nchunks; ++c) {
+                    if (c + 1 < nchunks) { stage(c + 1); fb_cp_async_wait<1>(); }
+                    else fb_cp_async_wait<0>();
+                    __syncthreads();
+                    if (active) {
+                        const int rows = min(KC, IN - c * KC);
+                        const double *ap = Ain + (size_t)c * KC * TM + m0;
+                        const double *wp = wst + (size_t)(c & 1) * KC * maxwp + n0;
+#pragma unroll 4
+                        for (int k = 0; k < rows; ++k, ap += TM, wp += OUTP) {
+                            const double2 a01 = *reinterpret_cast<const double2 *>(ap);
+                            const double2 a23 = *reinterpret_cast<const double2 *>(ap + 2);
+                            const double a[4] = {a01.x, a01.y, a23.x, a23.y};
+                            double w[8];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const double2 t = reinterpret_cast<const double2 *>(wp)[q];
+                                w[2 * q] = t.x; w[2 * q + 1] = t.y;
+                            }
+#pragma unroll
+                            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) acc[r][j] = __fma_rn(w[j], a[r], acc[r][j]);
+                        }
+                    }
+                    __syncthreads();                      // this stage is refilled two chunks from now
+                }
+                if (!active) continue;
+                // bias, ReLU, non-zero counts; hidden activations go to the other buffer
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int nn = n0 + j;
+                    const bool valid = nn < OUT;
+                    const double bj = valid ? __ldg(net.B + net.boff[l] + nn) : 0.0;
+                    uint32_t cnt = 0;
+                    double h[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const double pre = __dadd_rn(acc[r][j], bj);
+                        const bool pos = fb_pos(pre);
+                        const bool nz = (last ? fb_nonzero(pre) : pos) && (m0 + r < live) && valid;
+                        const uint32_t bal = __ballot_sync(0xffffffffu, nz);
+                        cnt += __popc(bal & (0xffu << (lane_n * 8)));
+                        h[r] = pos ? pre : 0.0;
+                    }
+                    if (valid) {
+                        if (lane_m == 0 && cnt) atomicAdd(&scnt[net.boff[l] + nn], cnt);
+                        if (!last) {
+                            double *op = Aout + (size_t)nn * TM + m0;
+                            *reinterpret_cast<double2 *>(op) = make_double2(h[0], h[1]);
+                            *reinterpret_cast<double2 *>(op + 2) = make_double2(h[2], h[3]);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        for (int k = tid; k < N; k += FB_TILE_THREADS) {
+            const uint32_t c = scnt[k];
+            if (c) atomicAdd(&counts[p * N + k], c);
+            scnt[k] = 0;
+        }
+        __syncthreads();
+    }
+}
+
 // weights (float64) staged once per CTA into dynamic shared memory: [P] weights, [N] biases, then
 // per-warp uint32 counters [warps][N].
 template <bool PHILOX>

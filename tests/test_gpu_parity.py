@@ -216,9 +216,11 @@ def test_subnormal_capable_model_takes_exact_sign_test(eng):
     assert want[:, 40:45].all()                # the last hidden layer is active with values below 2^-1042
 
 
-@pytest.mark.parametrize("name", ["AC-1", "AC-12", "GC-2", "BM-1"])
-def test_generic_kernels_agree_with_specialised(eng, name):
-    """FAIRIFY_B200_FORCE_GENERIC routes a specialised shape through the runtime-shape kernels (subprocess)."""
+@pytest.mark.parametrize("name,tiled", [("AC-1", "1"), ("AC-12", "1"), ("GC-2", "1"), ("BM-1", "1"), ("AC-1", "0"),
+                                        ("BM-1", "0"), ("BM-4", "0"), ("AC-5", "0")])
+def test_generic_kernels_agree_with_specialised(eng, name, tiled):
+    """FAIRIFY_B200_FORCE_GENERIC routes a specialised shape through the runtime-shape kernels (subprocess); the profile
+    goes through the tiled kernel, or with FAIRIFY_B200_TILED_PROFILE=0 through the sample-per-lane kernel."""
     import subprocess
     import sys
     code = f"""
@@ -242,7 +244,7 @@ assert np.array_equal(m.forward(X.astype(np.float64)).cpu().numpy(), O.forward_f
 assert np.array_equal(m.forward(X.astype(np.float32)).cpu().numpy(), O.forward_f32(net, X))
 print('generic-ok', m.specialised)
 """
-    env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1")
+    env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1", FAIRIFY_B200_TILED_PROFILE=tiled)
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "generic-ok" in out.stdout, out.stdout + out.stderr
 
