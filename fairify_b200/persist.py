@@ -12,7 +12,7 @@ import json
 
 import numpy as np
 
-FORMAT = 1
+FORMAT = 2        # 2: device sampler draws 4 / 2 / 1 features per Philox word by box class (files of format 1 are refused)
 
 
 def fingerprint(model, grid, S, seed, first, count):
