@@ -374,8 +374,8 @@ static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const vo
 }
 
 // Runtime-shape profile: the tiled kernel (fb_generic.cuh) for the big networks, the sample-per-lane kernel for the
-// rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane): BM-4 27 vs 11, AC-4 25 vs 13, AC-5 / BM-7 30 vs
-// 20, but GC-5 (a funnel of mostly narrow layers, 4004 weights) 19 vs 21 -- hence the weight-count threshold.
+// rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane): BM-4 30 vs 11, AC-4 28 vs 13, AC-5 / BM-7 32-33
+// vs 20, but GC-5 (a funnel of mostly narrow layers, 4004 weights) 19 vs 21 -- hence the weight-count threshold.
 // FAIRIFY_B200_TILED_PROFILE=1 / 0 forces one or the other (tests, comparisons).
 static bool fb_use_tiled_profile(const fb_model *m)
 {

@@ -83,7 +83,7 @@ struct FbGenCountVisit {
 // neurons) register tile whose 32 accumulators each run  acc = fma(w, x, acc)  over k ascending -- per neuron exactly
 // the chain of the oracle and of the other kernels, so the counts are bit-identical.  Per k a thread loads 4
 // activations (shared memory, the 4 lanes that share the samples read the same words) and 8 weights (shared memory
-// too: the layer's rows, padded to 32 columns, stream through two cp.async stages of 16 rows) for 32 multiply-adds,
+// too: the layer's rows, padded to 32 columns, stream through three cp.async stages of 16 rows) for 32 multiply-adds,
 // against one activation load per multiply-add of the sample-per-lane kernel below.
 // counts[p][N] is atomically added to (caller zeroes first).
 // ---------------------------------------------------------------------------------------------------
@@ -110,10 +110,11 @@ __device__ __forceinline__ void fb_cp_async_commit() { asm volatile("cp.async.co
 template <int N>
 __device__ __forceinline__ void fb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// dynamic shared memory: two activation buffers [maxw][TM], two weight stages [KC][maxwp], per-neuron counters [N]
+#define FB_TILE_STAGES 3         // weight stages in flight: with three, one barrier per stage suffices
+// dynamic shared memory: two activation buffers [maxw][TM], the weight stages [KC][maxwp], per-neuron counters [N]
 __host__ __device__ inline size_t fb_tile_smem_bytes(int maxw, int maxwp, int N, int TM)
 {
-    return sizeof(double) * (2 * (size_t)maxw * TM + 2 * (size_t)FB_TILE_KC * maxwp) + sizeof(uint32_t) * N;
+    return sizeof(double) * (2 * (size_t)maxw * TM + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp) + sizeof(uint32_t) * N;
 }
 
 template <int TM, bool PHILOX>
@@ -127,8 +128,8 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
     double *buf0 = reinterpret_cast<double *>(fb_smem);               // activations: two [maxw][TM] buffers
     const int bufsz = net.maxw * TM;
     const int maxwp = (net.maxw + 31) & ~31;
-    double *wst = buf0 + 2 * (size_t)bufsz;                            // weights: two [KC][maxwp] stages
-    uint32_t *scnt = reinterpret_cast<uint32_t *>(wst + 2 * (size_t)KC * maxwp);
+    double *wst = buf0 + 2 * (size_t)bufsz;                            // weights: FB_TILE_STAGES stages of [KC][maxwp]
+    uint32_t *scnt = reinterpret_cast<uint32_t *>(wst + (size_t)FB_TILE_STAGES * KC * maxwp);
     constexpr int MB = TM / 32;                           // 32-sample blocks of the tile
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lane_m = lane & 7, lane_n = lane >> 3;      // a warp's block: 8 lanes x 4 samples by 4 lanes x 8 neurons
@@ -189,7 +190,7 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
             auto stage = [&](int c) {
                 const int rows = min(KC, IN - c * KC);
                 const double2 *src = reinterpret_cast<const double2 *>(Wl + (size_t)c * KC * OUTP);
-                double2 *dst = reinterpret_cast<double2 *>(wst + (size_t)(c & 1) * KC * maxwp);
+                double2 *dst = reinterpret_cast<double2 *>(wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp);
                 for (int i = tid; i < rows * (OUTP / 2); i += FB_TILE_THREADS) fb_cp_async16(dst + i, src + i);
                 fb_cp_async_commit();
             };
@@ -197,40 +198,58 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
                 const int blk = blk0 + warp;
                 const bool active = blk < nblocks;
                 const int mb = blk % MB, nb = blk / MB;
-                const int m0 = mb * 32 + lane_m * 4, n0 = nb * 32 + lane_n * 8;
+                // this thread's 4 samples: two adjacent pairs 16 apart, m0 + {0, 1, 16, 17} -- a quarter-warp then reads
+                // 128 contiguous bytes per 128-bit load (no bank conflicts); its 8 neurons: n0 .. n0 + 7
+                const int m0 = mb * 32 + lane_m * 2, n0 = nb * 32 + lane_n * 8;
                 double acc[4][8];
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
 #pragma unroll
                     for (int j = 0; j < 8; ++j) acc[r][j] = 0.0;
+                // stage c is consumed in iteration c while c+1 and c+2 are in flight; the barrier at the top of an
+                // iteration also says that everybody is done with stage c-1, whose slot stage c+2 is about to overwrite
                 stage(0);
+                if (nchunks > 1) stage(1);
                 for (int c = 0; c < nchunks; ++c) {
-                    if (c + 1 < nchunks) { stage(c + 1); fb_cp_async_wait<1>(); }
+                    if (c + 1 < nchunks) fb_cp_async_wait<1>();
                     else fb_cp_async_wait<0>();
                     __syncthreads();
+                    if (c + 2 < nchunks) stage(c + 2);
                     if (active) {
                         const int rows = min(KC, IN - c * KC);
                         const double *ap = Ain + (size_t)c * KC * TM + m0;
-                        const double *wp = wst + (size_t)(c & 1) * KC * maxwp + n0;
-#pragma unroll 4
-                        for (int k = 0; k < rows; ++k, ap += TM, wp += OUTP) {
-                            const double2 a01 = *reinterpret_cast<const double2 *>(ap);
-                            const double2 a23 = *reinterpret_cast<const double2 *>(ap + 2);
-                            const double a[4] = {a01.x, a01.y, a23.x, a23.y};
-                            double w[8];
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const double2 t = reinterpret_cast<const double2 *>(wp)[q];
-                                w[2 * q] = t.x; w[2 * q + 1] = t.y;
+                        const double *wp = wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp + n0;
+                        // operands of row k+1 are fetched while row k's multiply-adds issue (two register sets, A / B)
+                        double2 xa[2], wa[4], xb[2], wb[4];
+#define FB_TILE_LOAD(X, W, AP, WP)                                                                         \
+    {                                                                                                       \
+        X[0] = *reinterpret_cast<const double2 *>(AP); X[1] = *reinterpret_cast<const double2 *>((AP) + 16); \
+        W[0] = reinterpret_cast<const double2 *>(WP)[0]; W[1] = reinterpret_cast<const double2 *>(WP)[1];   \
+        W[2] = reinterpret_cast<const double2 *>(WP)[2]; W[3] = reinterpret_cast<const double2 *>(WP)[3];   \
+    }
+#define FB_TILE_FMA(X, W)                                                                                  \
+    {                                                                                                       \
+        const double a_[4] = {X[0].x, X[0].y, X[1].x, X[1].y};                                              \
+        const double w_[8] = {W[0].x, W[0].y, W[1].x, W[1].y, W[2].x, W[2].y, W[3].x, W[3].y};              \
+        _Pragma("unroll") for (int r = 0; r < 4; ++r)                                                       \
+            _Pragma("unroll") for (int j = 0; j < 8; ++j) acc[r][j] = __fma_rn(w_[j], a_[r], acc[r][j]);    \
+    }
+                        FB_TILE_LOAD(xa, wa, ap, wp);
+                        for (int k = 0; k < rows; k += 2) {
+                            const bool odd = k + 1 < rows, more = k + 2 < rows;
+                            if (odd) FB_TILE_LOAD(xb, wb, ap + TM, wp + OUTP);
+                            FB_TILE_FMA(xa, wa);
+                            ap += 2 * TM; wp += 2 * OUTP;
+                            if (odd) {
+                                if (more) FB_TILE_LOAD(xa, wa, ap, wp);
+                                FB_TILE_FMA(xb, wb);
                             }
-#pragma unroll
-                            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) acc[r][j] = __fma_rn(w[j], a[r], acc[r][j]);
                         }
+#undef FB_TILE_LOAD
+#undef FB_TILE_FMA
                     }
-                    __syncthreads();                      // this stage is refilled two chunks from now
                 }
+                __syncthreads();                          // the next round (or layer) restarts the stages
                 if (!active) continue;
                 // bias, ReLU, non-zero counts; hidden activations go to the other buffer
 #pragma unroll
@@ -244,7 +263,7 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
                     for (int r = 0; r < 4; ++r) {
                         const double pre = __dadd_rn(acc[r][j], bj);
                         const bool pos = fb_pos(pre);
-                        const bool nz = (last ? fb_nonzero(pre) : pos) && (m0 + r < live) && valid;
+                        const bool nz = (last ? fb_nonzero(pre) : pos) && (m0 + (r >> 1) * 16 + (r & 1) < live) && valid;
                         const uint32_t bal = __ballot_sync(0xffffffffu, nz);
                         cnt += __popc(bal & (0xffu << (lane_n * 8)));
                         h[r] = pos ? pre : 0.0;
@@ -254,7 +273,7 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
                         if (!last) {
                             double *op = Aout + (size_t)nn * TM + m0;
                             *reinterpret_cast<double2 *>(op) = make_double2(h[0], h[1]);
-                            *reinterpret_cast<double2 *>(op + 2) = make_double2(h[2], h[3]);
+                            *reinterpret_cast<double2 *>(op + 16) = make_double2(h[2], h[3]);
                         }
                     }
                 }
