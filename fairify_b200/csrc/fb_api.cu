@@ -66,6 +66,7 @@ struct fb_model {
     void *p64 = nullptr, *p32 = nullptr;
     FbTileNet tile{};               // padded float64 weights for the tiled profile kernel
     double *dWpad = nullptr;
+    float *dWpad32 = nullptr;
 };
 
 // The specialised profile kernel tests "pre-activation > 0" on the high word of the double, which misreads positive
@@ -117,7 +118,7 @@ extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32);
     delete m;
 }
 
@@ -183,7 +184,12 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         e = cudaMalloc(&m->dWpad, sizeof(double) * wp.size());
         if (e == cudaSuccess) e = cudaMemcpy(m->dWpad, wp.data(), sizeof(double) * wp.size(), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
-        t.Wp = m->dWpad; t.B = m->dB64;
+        std::vector<float> wp32(wp.size());
+        for (size_t k = 0; k < wp.size(); ++k) wp32[k] = (float)wp[k];                 // exact: the weights are float32 values
+        e = cudaMalloc(&m->dWpad32, sizeof(float) * wp32.size());
+        if (e == cudaSuccess) e = cudaMemcpy(m->dWpad32, wp32.data(), sizeof(float) * wp32.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
+        t.Wp = m->dWpad; t.B = m->dB64; t.Wp32 = m->dWpad32; t.B32 = m->dB32;
     }
     m->spec = fb_find_spec(L, dims);
     if (m->spec && !fb_model_subnormal_free(g, m->hW64, m->hB64)) m->spec = nullptr;   // runtime-shape kernels: exact sign test
@@ -413,6 +419,33 @@ static int fb_profile_tiled(const fb_model *m, int64_t n, const int32_t *boxes, 
     const size_t smem128 = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, 128);
     if (smem128 <= 220 * 1024) return fb_profile_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, counts, st);
     return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
+}
+
+template <int TM>
+static int fb_screen_tiled_launch(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                  uint64_t seed, int64_t first_index, int pa_col, unsigned long long *key, cudaStream_t st)
+{
+    const size_t smem = fb_screen_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, TM);
+    if (samples == nullptr) {
+        auto k = fb_screen_tile_kernel<TM, true>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_TILE_THREADS, smem, n, m->num_sms), FB_TILE_THREADS, smem, st>>>(
+            m->tile, n, boxes, samples, seed, first_index, S, pa_col, key);
+    } else {
+        auto k = fb_screen_tile_kernel<TM, false>;
+        FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k<<<fb_grid_for(k, FB_TILE_THREADS, smem, n, m->num_sms), FB_TILE_THREADS, smem, st>>>(
+            m->tile, n, boxes, samples, seed, first_index, S, pa_col, key);
+    }
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+static int fb_screen_tiled(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                           int64_t first_index, int pa_col, unsigned long long *key, cudaStream_t st)
+{
+    // 64-row tiles keep two CTAs on an SM (float activations are half the size) and waste less of the last tile
+    return fb_screen_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, pa_col, key, st);
 }
 
 static size_t fb_profile_gen_smem(const fb_model *m)
@@ -711,6 +744,8 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
     if (fb_use_spec(m)) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, (unsigned long long *)key.p, m->num_sms, st));
+    } else if (fb_use_tiled_profile(m)) {
+        if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, (unsigned long long *)key.p, st)) return rc;
     } else {
         const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
         if (samples == nullptr) {

@@ -96,6 +96,8 @@ struct FbTileNet {
     int maxw;                        // widest layer (inputs included): pitch of the activation buffers is TM
     const double *Wp;                // [in][dimsp[l+1]] per layer, zero padded
     const double *B;
+    const float *Wp32;               // the same in float32 (partition screen)
+    const float *B32;
 };
 
 #define FB_TILE_THREADS 256
@@ -285,6 +287,199 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
             if (c) atomicAdd(&counts[p * N + k], c);
             scnt[k] = 0;
         }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Per-partition sampled counterexample screen for wide runtime-shape networks, float32, organised like the tiled
+// profile kernel above: the rows of the product are (sample, protected value) pairs.  One CTA per partition walks
+// the samples in tiles of TM rows and stops at the first tile that holds a counterexample, so the answer -- the
+// lowest sample index whose sweep of the protected column produces both classes, with the first positive and the
+// first negative value -- is the one the sample-per-lane kernel gives.  A sweep wider than a tile is cut into
+// segments of TM values of one sample.
+// ---------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t fb_screen_tile_smem_bytes(int maxw, int maxwp, int TM)
+{
+    return sizeof(float) * (2 * (size_t)maxw * TM + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp) + 64;
+}
+
+// all layers for the TM rows in buf0 (feature-major); returns the buffer whose first row holds the TM logits
+template <int TM>
+__device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net, float *buf0, int bufsz, float *wst, int maxwp)
+{
+    constexpr int KC = FB_TILE_KC, MB = TM / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lane_m = lane & 7, lane_n = lane >> 3;
+    for (int l = 0; l < net.L; ++l) {
+        const int IN = net.dims[l], OUT = net.dims[l + 1], OUTP = net.dimsp[l + 1];
+        const bool last = (l == net.L - 1);
+        const float *Ain = buf0 + (l & 1) * bufsz;
+        float *Aout = buf0 + ((l + 1) & 1) * bufsz;
+        const float *Wl = net.Wp32 + net.woffp[l];
+        if (OUT <= 8) {
+            for (int t = tid; t < TM * OUT; t += FB_TILE_THREADS) {
+                const int mm = t % TM, nn = t / TM;
+                const float *ap = Ain + mm;
+                const float *wp = Wl + nn;
+                float acc = 0.0f;
+#pragma unroll 4
+                for (int k = 0; k < IN; ++k) acc = __fmaf_rn(__ldg(wp + (size_t)k * OUTP), ap[(size_t)k * TM], acc);
+                const float pre = __fadd_rn(acc, __ldg(net.B32 + net.boff[l] + nn));
+                Aout[(size_t)nn * TM + mm] = last ? pre : (fb_pos(pre) ? pre : 0.0f);
+            }
+            __syncthreads();
+            continue;
+        }
+        const int nblocks = MB * (OUTP / 32);
+        const int nchunks = (IN + KC - 1) / KC;
+        auto stage = [&](int c) {
+            const int rows = min(KC, IN - c * KC);
+            const float4 *src = reinterpret_cast<const float4 *>(Wl + (size_t)c * KC * OUTP);
+            float4 *dst = reinterpret_cast<float4 *>(wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp);
+            for (int i = tid; i < rows * (OUTP / 4); i += FB_TILE_THREADS) fb_cp_async16(dst + i, src + i);
+            fb_cp_async_commit();
+        };
+        for (int blk0 = 0; blk0 < nblocks; blk0 += FB_TILE_THREADS / 32) {
+            const int blk = blk0 + warp;
+            const bool active = blk < nblocks;
+            const int mb = blk % MB, nb = blk / MB;
+            const int m0 = mb * 32 + lane_m * 4, n0 = nb * 32 + lane_n * 8;      // 4 adjacent rows, 8 adjacent neurons
+            float acc[4][8];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[r][j] = 0.0f;
+            stage(0);
+            if (nchunks > 1) stage(1);
+            for (int c = 0; c < nchunks; ++c) {
+                if (c + 1 < nchunks) fb_cp_async_wait<1>();
+                else fb_cp_async_wait<0>();
+                __syncthreads();
+                if (c + 2 < nchunks) stage(c + 2);
+                if (active) {
+                    const int rows = min(KC, IN - c * KC);
+                    const float *ap = Ain + (size_t)c * KC * TM + m0;
+                    const float *wp = wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp + n0;
+#pragma unroll 4
+                    for (int k = 0; k < rows; ++k, ap += TM, wp += OUTP) {
+                        const float4 a4 = *reinterpret_cast<const float4 *>(ap);
+                        const float4 w0 = reinterpret_cast<const float4 *>(wp)[0], w1 = reinterpret_cast<const float4 *>(wp)[1];
+                        const float a[4] = {a4.x, a4.y, a4.z, a4.w};
+                        const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) acc[r][j] = __fmaf_rn(w[j], a[r], acc[r][j]);
+                    }
+                }
+            }
+            __syncthreads();
+            if (!active) continue;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int nn = n0 + j;
+                if (nn < OUT) {
+                    const float bj = __ldg(net.B32 + net.boff[l] + nn);
+                    float h[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const float pre = __fadd_rn(acc[r][j], bj);
+                        h[r] = last ? pre : (fb_pos(pre) ? pre : 0.0f);
+                    }
+                    *reinterpret_cast<float4 *>(Aout + (size_t)nn * TM + m0) = make_float4(h[0], h[1], h[2], h[3]);
+                }
+            }
+        }
+        __syncthreads();
+    }
+    return buf0 + (net.L & 1) * bufsz;
+}
+
+template <int TM, bool PHILOX>
+__global__ void __launch_bounds__(FB_TILE_THREADS)
+fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict__ boxes,
+                      const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp, int pa_col,
+                      unsigned long long *__restrict__ ce_key)
+{
+    extern __shared__ __align__(16) unsigned char fb_smem[];
+    float *buf0 = reinterpret_cast<float *>(fb_smem);
+    const int bufsz = net.maxw * TM;
+    const int maxwp = (net.maxw + 31) & ~31;
+    float *wst = buf0 + 2 * (size_t)bufsz;
+    unsigned long long *s_best = reinterpret_cast<unsigned long long *>(wst + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp);
+    int *s_state = reinterpret_cast<int *>(s_best + 1);                 // havep, vp, haven, vn of a segmented sweep
+    const int tid = threadIdx.x;
+    const int D0 = net.dims[0];
+    for (int64_t p = blockIdx.x; p < n; p += gridDim.x) {
+        const int32_t *box = boxes + p * (2 * D0);
+        const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
+        const int W = pa_hi - pa_lo + 1;
+        const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
+        const int64_t pidx = first_index + p;
+        if (tid == 0) *s_best = ~0ull;
+        __syncthreads();
+        // row t of a tile: sample s_row, protected value v_row (or a zero row past the end)
+        auto fill = [&](int s_row, int v_row, bool exists) {
+            float *col = buf0 + tid;
+            if (exists) {
+                if (PHILOX) fb_draw_row<float>(box, D0, grp, (uint32_t)s_row, pidx, seed, col, TM);
+                else {
+                    const int32_t *row = samples + ((int64_t)p * nsamp + s_row) * D0;
+                    for (int i = 0; i < D0; ++i) col[(size_t)i * TM] = (float)__ldg(row + i);
+                }
+                col[(size_t)pa_col * TM] = (float)v_row;
+            } else {
+                for (int i = 0; i < D0; ++i) col[(size_t)i * TM] = 0.0f;
+            }
+        };
+        if (W <= TM) {
+            const int spt = TM / W;                                       // whole samples per tile
+            for (int sbase = 0; sbase < nsamp; sbase += spt) {
+                const int ns = min(spt, nsamp - sbase);
+                if (tid < TM) fill(sbase + tid / W, pa_lo + tid % W, tid < ns * W);
+                __syncthreads();
+                const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
+                if (tid < ns) {
+                    bool havep = false, haven = false;
+                    int vp = 0, vn = 0;
+                    for (int vi = 0; vi < W; ++vi) {
+                        const float yv = y[tid * W + vi];
+                        if (yv > 0.0f && !havep) { havep = true; vp = vi; }
+                        if (yv < 0.0f && !haven) { haven = true; vn = vi; }
+                    }
+                    if (havep && haven)
+                        atomicMin(s_best, ((unsigned long long)(uint32_t)(sbase + tid) << 32) |
+                                              ((unsigned long long)(uint32_t)vp << 16) | (unsigned long long)(uint32_t)vn);
+                }
+                __syncthreads();
+                if (*s_best != ~0ull) break;
+            }
+        } else {
+            for (int s = 0; s < nsamp; ++s) {
+                if (tid == 0) { s_state[0] = 0; s_state[1] = 0; s_state[2] = 0; s_state[3] = 0; }
+                for (int v0 = 0; v0 < W; v0 += TM) {
+                    const int nv = min(TM, W - v0);
+                    if (tid < TM) fill(s, pa_lo + v0 + tid, tid < nv);
+                    __syncthreads();
+                    const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
+                    if (tid == 0) {
+                        for (int vi = 0; vi < nv; ++vi) {
+                            const float yv = y[vi];
+                            if (yv > 0.0f && !s_state[0]) { s_state[0] = 1; s_state[1] = v0 + vi; }
+                            if (yv < 0.0f && !s_state[2]) { s_state[2] = 1; s_state[3] = v0 + vi; }
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (tid == 0 && s_state[0] && s_state[2])
+                    *s_best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)s_state[1] << 16) |
+                              (unsigned long long)(uint32_t)s_state[3];
+                __syncthreads();
+                if (*s_best != ~0ull) break;
+            }
+        }
+        if (tid == 0 && *s_best != ~0ull) ce_key[p] = *s_best;
         __syncthreads();
     }
 }
