@@ -417,6 +417,9 @@ static int fb_profile_tiled(const fb_model *m, int64_t n, const int32_t *boxes, 
     if (!already_zeroed) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));   // the kernel adds
     // 128 samples per CTA when the activation buffers of that height fit beside the weight stages, else 64
     const size_t smem128 = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, 128);
+    static const int forced_tm = [] { const char *v = getenv("FAIRIFY_B200_TILE_TM"); return v ? atoi(v) : 0; }();   // tuning aid
+    if (forced_tm == 32) return fb_profile_tiled_launch<32>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    if (forced_tm == 64) return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
     if (smem128 <= 220 * 1024) return fb_profile_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, counts, st);
     return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
 }
