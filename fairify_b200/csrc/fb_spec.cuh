@@ -21,8 +21,13 @@
 // inputs of layer l plus the accumulators of layer l+1 -- e.g. 13 + 1 values for a 13-100-1 network instead
 // of 13 + 100.
 #ifndef FB_SPEC_JB
-#define FB_SPEC_JB 1
+#define FB_SPEC_JB 1            // neurons evaluated side by side when a thread carries two samples
 #endif
+// ... and when it carries one (then a neuron's dot product is the only chain in flight): 8 for layers of 64 neurons or
+// more, else 4.  Measured on B200, % of FP64 peak for blocks of 1 / 2 / 4 / 8: BM-1 (16-64-16-1) 38 / 39 / 42 / 51,
+// BM-8 42 / 41 / 48 / 48, AC-7 49 / 49 / 51 / 51, BM-2 (16-32-16-1) 58 / 62 / 61 / 55.
+template <typename T> struct FbOneSample { static constexpr bool value = false; };
+template <> struct FbOneSample<VecD<1>> { static constexpr bool value = true; };
 template <class S, int l, typename T, class PRM, class Visit>
 __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
 {
@@ -34,9 +39,10 @@ __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim
 #pragma unroll
     for (int k = 0; k < M2; ++k) acc2[k] = T(0.0);
     T h = T(0.0);
-    // neurons of layer l in blocks of JB (independent dot products side by side).  Measured on B200: 1, 2, 4 and 8
-    // give the same rate -- ptxas interleaves neighbouring neurons' chains by itself -- so 1 it stays.
-    constexpr int JB = FB_SPEC_JB;
+    // neurons of layer l in blocks of JB (independent dot products side by side).  With two samples per thread ptxas
+    // interleaves neighbouring neurons' chains by itself (1, 2, 4, 8 measured the same on B200); with one sample per
+    // thread it leaves each dot product a serial chain of ~20-cycle multiply-adds unless the source spells the block out.
+    constexpr int JB = FbOneSample<T>::value ? (M >= 64 ? 8 : 4) : FB_SPEC_JB;
 #pragma unroll
     for (int j0 = 0; j0 < M; j0 += JB) {
         T acc[JB];

@@ -348,6 +348,40 @@ def test_prune_host_roundtrip_equals_device(eng):
         assert np.array_equal(out[k].numpy(), r.numpy(k)), k
 
 
+def test_prune_host_pipeline_slices_equal_device():
+    """fb_prune_host cuts a batch into slices and overlaps upload / kernels / download on three streams; with the slice
+    size forced down to 700 partitions (ragged last slice, injected samples too) every output must equal the
+    device-resident run (subprocess: the slice size is read once per process)."""
+    import subprocess
+    import sys
+    code = f"""
+import numpy as np, sys, torch
+sys.path.insert(0, {os.path.dirname(os.path.dirname(os.path.abspath(__file__)))!r})
+from tests.common import Golden
+from fairify_b200 import engine
+from oracle import oracle as O
+G = Golden()
+for name in ("AC-1", "BM-4"):
+    w, b = G.wb(name); m = engine.Model(w, b); dom = G.domain(name)
+    grid = engine.Grid(dom.columns, dom.ranges, 10 if name == "AC-1" else dom.threshold)
+    n = min(3005, len(grid)); boxes = grid.boxes(0, n)
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    tol = engine.sliver_tolerance(w, b, lo, hi)
+    r = m.prune(boxes, S=48, seed=9, first_index=11, tol=tol, want=engine.ALL_OUTPUTS)
+    out = m.prune_host(boxes.cpu().pin_memory(), S=48, seed=9, first_index=11, tol=tol, want=engine.ALL_OUTPUTS)
+    for k in engine.ALL_OUTPUTS:
+        assert np.array_equal(out[k].numpy(), r.numpy(k)), (name, k)
+    samples = O.philox_samples(9, 11, boxes.cpu().numpy(), 48)
+    out2 = m.prune_host(boxes.cpu(), samples=torch.as_tensor(samples), tol=tol)        # pageable host memory
+    for k in ("dead", "verdict", "counts"):
+        assert np.array_equal(out2[k].numpy(), r.numpy(k)), (name, k, "injected")
+print("pipeline-ok")
+"""
+    env = dict(os.environ, FAIRIFY_B200_HOST_SLICE="700")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0 and "pipeline-ok" in out.stdout, out.stdout + out.stderr
+
+
 def test_empty_batch_and_bad_arguments(eng):
     w, b = G.wb("GC-3")
     m = eng.Model(w, b)
