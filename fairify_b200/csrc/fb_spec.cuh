@@ -26,6 +26,13 @@
 // ... and when it carries one (then a neuron's dot product is the only chain in flight): 8 for layers of 64 neurons or
 // more, else 4.  Measured on B200, % of FP64 peak for blocks of 1 / 2 / 4 / 8: BM-1 (16-64-16-1) 38 / 39 / 42 / 51,
 // BM-8 42 / 41 / 48 / 48, AC-7 49 / 49 / 51 / 51, BM-2 (16-32-16-1) 58 / 62 / 61 / 55.
+// Per-shape choices that only change ptxas' schedule, taken from measurements on B200 (tools/time_profile.py, % of
+// FP64 peak): neuron block for two-sample shapes, and whether the box waits in shared memory for shapes above 64 neurons.
+//   13-100-1 (AC-2): block 1 / 2 / 4 = 63 / 64 / 71, shared-memory box 63     20-100-1 (GC-2): 63 / 62 / 53, box 72
+//   16-100-1 (BM-3): 70 / 69 / 70, box 63
+template <class S> struct FbTune { static constexpr int jb2 = FB_SPEC_JB; static constexpr bool smem_box_wide = false; };
+template <> struct FbTune<Spec<13, 100, 1>> { static constexpr int jb2 = 4; static constexpr bool smem_box_wide = false; };
+template <> struct FbTune<Spec<20, 100, 1>> { static constexpr int jb2 = FB_SPEC_JB; static constexpr bool smem_box_wide = true; };
 template <typename T> struct FbOneSample { static constexpr bool value = false; };
 template <> struct FbOneSample<VecD<1>> { static constexpr bool value = true; };
 template <class S, int l, typename T, class PRM, class Visit>
@@ -42,7 +49,7 @@ __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim
     // neurons of layer l in blocks of JB (independent dot products side by side).  With two samples per thread ptxas
     // interleaves neighbouring neurons' chains by itself (1, 2, 4, 8 measured the same on B200); with one sample per
     // thread it leaves each dot product a serial chain of ~20-cycle multiply-adds unless the source spells the block out.
-    constexpr int JB = FbOneSample<T>::value ? (M >= 64 ? 8 : 4) : FB_SPEC_JB;
+    constexpr int JB = FbOneSample<T>::value ? (M >= 64 ? 8 : 4) : FbTune<S>::jb2;
 #pragma unroll
     for (int j0 = 0; j0 < M; j0 += JB) {
         T acc[JB];
@@ -114,6 +121,9 @@ struct FbMaskedVisit {
 #endif
 #ifndef FB_PROFILE_SMEM_BOX
 #define FB_PROFILE_SMEM_BOX 1
+#endif
+#ifndef FB_PROFILE_SMEM_BOX_MAXN
+#define FB_PROFILE_SMEM_BOX_MAXN 64
 #endif
 #ifndef FB_PROFILE_MINB
 #define FB_PROFILE_MINB 1                                // one 512-thread CTA per SM: caps registers at 128
@@ -239,7 +249,7 @@ __host__ __device__ constexpr int fb_profile_spt()
 template <class S>
 __host__ __device__ constexpr bool fb_profile_smem_box()
 {
-    return FB_PROFILE_SMEM_BOX && S::N <= 64;
+    return FB_PROFILE_SMEM_BOX && (S::N <= FB_PROFILE_SMEM_BOX_MAXN || FbTune<S>::smem_box_wide);
 }
 
 // The one-instruction sign test pays for the small shapes; on the 100-wide and the deep funnel shapes it changes
