@@ -35,6 +35,7 @@ template <> struct FbTune<Spec<13, 100, 1>> { static constexpr int jb2 = 4; stat
 template <> struct FbTune<Spec<20, 100, 1>> { static constexpr int jb2 = FB_SPEC_JB; static constexpr bool smem_box_wide = true; };
 template <typename T> struct FbOneSample { static constexpr bool value = false; };
 template <> struct FbOneSample<VecD<1>> { static constexpr bool value = true; };
+// (the row-per-thread float kernels -- screens, logits -- measured the same with and without blocks)
 template <class S, int l, typename T, class PRM, class Visit>
 __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim(l)], Visit &v)
 {
