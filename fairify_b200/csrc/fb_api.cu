@@ -612,6 +612,11 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
             return rc;
         }
     } events;
+    // whatever way this function is left, nothing issued on the three streams may outlive the buffers
+    struct Drain {
+        cudaStream_t a, b, c;
+        ~Drain() { cudaStreamSynchronize(a); cudaStreamSynchronize(b); cudaStreamSynchronize(c); }
+    } drain{up, st, down};
     cudaEvent_t ready;                                   // allocations (and tol) are in place on `st`
     FB_CUDA(events.make(&ready));
     FB_CUDA(cudaEventRecord(ready, st));

@@ -17,7 +17,8 @@
  *   samples   int32 [n][S][d], or NULL to draw them on the device: Philox4x32-10, counter = (sample,
  *             partition index, block), key = seed; each 32-bit word yields 4, 2 or 1 bounded integers (multiply-
  *             shift, the low half of the product handed on) depending on whether the box's widest range is
- *             <= 16, <= 256 or larger, so every value is uniform to within 2^-16 relative
+ *             <= 16, <= 256 or larger, so every value is uniform to within 2^-16 relative.  A feature's range
+ *             hi - lo + 1 must fit in 32 bits (hi - lo < 2^32 - 1)
  *   masks     uint32 [n][NW], NW = ceil(N/32); bit k = neuron k, neurons numbered layer by layer,
  *             output neuron included (N = sum of layer widths)
  *   per-neuron arrays  [n][N] in the same numbering
