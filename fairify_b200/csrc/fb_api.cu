@@ -379,30 +379,32 @@ static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const vo
     return FB_OK;
 }
 
-// Runtime-shape profile: the tiled kernel (fb_generic.cuh) for the big networks, the sample-per-lane kernel for the
-// rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane): BM-4 30 vs 11, AC-4 28 vs 13, AC-5 / BM-7 32-33
-// vs 20, but GC-5 (a funnel of mostly narrow layers, 4004 weights) 19 vs 21 -- hence the weight-count threshold.
+// Runtime-shape profile and partition screen: the tiled kernels (fb_generic.cuh) for the big networks, the sample-per-
+// lane kernels for the rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane profile): BM-4 30 vs 11, AC-4
+// 28 vs 13, AC-5 / BM-7 37 vs 20, GC-5 (a funnel of mostly narrow layers, 4004 weights) 23 vs 21; small networks forced
+// onto this path lose (AC-1 6 %), hence the weight-count threshold.
 // FAIRIFY_B200_TILED_PROFILE=1 / 0 forces one or the other (tests, comparisons).
 static bool fb_use_tiled_profile(const fb_model *m)
 {
     static const int forced = [] { const char *v = getenv("FAIRIFY_B200_TILED_PROFILE"); return !v ? -1 : (v[0] == '0' ? 0 : 1); }();
     if (forced >= 0) return forced == 1;
-    return m->gen.P >= 4500;
+    return m->gen.P >= 4000;
 }
 
-template <int TM>
+template <int TM, bool RESIDENT>
 static int fb_profile_tiled_launch(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                                    uint64_t seed, int64_t first_index, uint32_t *counts, cudaStream_t st)
 {
-    const size_t smem = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, TM);
+    const size_t smem = RESIDENT ? fb_tile_smem_bytes_resident(m->tile.maxw, m->tile.woffp[m->tile.L], m->gen.N, TM)
+                                 : fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, TM);
     const int64_t units = n * ((S + TM - 1) / TM);
     if (samples == nullptr) {
-        auto k = fb_profile_tile_kernel<TM, true>;
+        auto k = fb_profile_tile_kernel<TM, true, RESIDENT>;
         FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k<<<fb_grid_for(k, FB_TILE_THREADS, smem, units, m->num_sms), FB_TILE_THREADS, smem, st>>>(
             m->tile, n, boxes, samples, seed, first_index, S, counts);
     } else {
-        auto k = fb_profile_tile_kernel<TM, false>;
+        auto k = fb_profile_tile_kernel<TM, false, RESIDENT>;
         FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k<<<fb_grid_for(k, FB_TILE_THREADS, smem, units, m->num_sms), FB_TILE_THREADS, smem, st>>>(
             m->tile, n, boxes, samples, seed, first_index, S, counts);
@@ -415,13 +417,17 @@ static int fb_profile_tiled(const fb_model *m, int64_t n, const int32_t *boxes, 
                             int64_t first_index, uint32_t *counts, bool already_zeroed, cudaStream_t st)
 {
     if (!already_zeroed) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));   // the kernel adds
-    // 128 samples per CTA when the activation buffers of that height fit beside the weight stages, else 64
-    const size_t smem128 = fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, 128);
+    const size_t limit = 220 * 1024;
     static const int forced_tm = [] { const char *v = getenv("FAIRIFY_B200_TILE_TM"); return v ? atoi(v) : 0; }();   // tuning aid
-    if (forced_tm == 32) return fb_profile_tiled_launch<32>(m, n, boxes, samples, S, seed, first_index, counts, st);
-    if (forced_tm == 64) return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
-    if (smem128 <= 220 * 1024) return fb_profile_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, counts, st);
-    return fb_profile_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    if (forced_tm == 32) return fb_profile_tiled_launch<32, false>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    if (forced_tm == 64) return fb_profile_tiled_launch<64, false>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    // 128 samples per CTA with all weights resident in shared memory when that fits (networks up to ~64 wide), else
+    // 128 samples with staged weights, else 64 samples with staged weights (widths above 100)
+    if (fb_tile_smem_bytes_resident(m->tile.maxw, m->tile.woffp[m->tile.L], m->gen.N, 128) <= limit && forced_tm != 128)
+        return fb_profile_tiled_launch<128, true>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    if (fb_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, m->gen.N, 128) <= limit)
+        return fb_profile_tiled_launch<128, false>(m, n, boxes, samples, S, seed, first_index, counts, st);
+    return fb_profile_tiled_launch<64, false>(m, n, boxes, samples, S, seed, first_index, counts, st);
 }
 
 template <int TM>

@@ -118,8 +118,15 @@ __host__ __device__ inline size_t fb_tile_smem_bytes(int maxw, int maxwp, int N,
 {
     return sizeof(double) * (2 * (size_t)maxw * TM + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp) + sizeof(uint32_t) * N;
 }
+// ... with all `wdoubles` padded weights resident instead of the stages
+__host__ __device__ inline size_t fb_tile_smem_bytes_resident(int maxw, int wdoubles, int N, int TM)
+{
+    return sizeof(double) * (2 * (size_t)maxw * TM + (size_t)wdoubles) + sizeof(uint32_t) * N;
+}
 
-template <int TM, bool PHILOX>
+// RESIDENT: the whole padded weight array fits in shared memory beside the activations and is loaded once per CTA;
+// layers then run without stages and without the per-stage barriers.
+template <int TM, bool PHILOX, bool RESIDENT>
 __global__ void __launch_bounds__(FB_TILE_THREADS)
 fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict__ boxes,
                        const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp,
@@ -130,8 +137,14 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
     double *buf0 = reinterpret_cast<double *>(fb_smem);               // activations: two [maxw][TM] buffers
     const int bufsz = net.maxw * TM;
     const int maxwp = (net.maxw + 31) & ~31;
-    double *wst = buf0 + 2 * (size_t)bufsz;                            // weights: FB_TILE_STAGES stages of [KC][maxwp]
-    uint32_t *scnt = reinterpret_cast<uint32_t *>(wst + (size_t)FB_TILE_STAGES * KC * maxwp);
+    double *wst = buf0 + 2 * (size_t)bufsz;                            // weights: FB_TILE_STAGES stages of [KC][maxwp], or all of them
+    const size_t wdoubles = RESIDENT ? (size_t)net.woffp[net.L] : (size_t)FB_TILE_STAGES * KC * maxwp;
+    uint32_t *scnt = reinterpret_cast<uint32_t *>(wst + wdoubles);
+    if (RESIDENT) {
+        const double2 *src = reinterpret_cast<const double2 *>(net.Wp);
+        double2 *dst = reinterpret_cast<double2 *>(wst);
+        for (int i = threadIdx.x; i < net.woffp[net.L] / 2; i += FB_TILE_THREADS) dst[i] = __ldg(src + i);
+    }
     constexpr int MB = TM / 32;                           // 32-sample blocks of the tile
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lane_m = lane & 7, lane_n = lane >> 3;      // a warp's block: 8 lanes x 4 samples by 4 lanes x 8 neurons
@@ -166,7 +179,7 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
             const double *Ain = buf0 + (l & 1) * bufsz;
             double *Aout = buf0 + ((l + 1) & 1) * bufsz;
             const int nblocks = MB * (OUTP / 32);
-            const int nchunks = (IN + KC - 1) / KC;
+            const int nchunks = RESIDENT ? 1 : (IN + KC - 1) / KC;
             const double *Wl = net.Wp + net.woffp[l];
             if (OUT <= 8) {
                 // narrow layer (the logit, the tail of a funnel): a 32-column block would be mostly padding, so every
@@ -174,10 +187,10 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
                 for (int t = tid; t < TM * OUT; t += FB_TILE_THREADS) {
                     const int mm = t % TM, nn = t / TM;
                     const double *ap = Ain + mm;
-                    const double *wp = Wl + nn;
+                    const double *wp = (RESIDENT ? wst + net.woffp[l] : Wl) + nn;
                     double acc = 0.0;
 #pragma unroll 4
-                    for (int k = 0; k < IN; ++k) acc = __fma_rn(__ldg(wp + (size_t)k * OUTP), ap[(size_t)k * TM], acc);
+                    for (int k = 0; k < IN; ++k) acc = __fma_rn(wp[(size_t)k * OUTP], ap[(size_t)k * TM], acc);
                     const double pre = __dadd_rn(acc, __ldg(net.B + net.boff[l] + nn));
                     const bool pos = fb_pos(pre);
                     const bool nz = (last ? fb_nonzero(pre) : pos) && (mm < live);
@@ -210,17 +223,21 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
                     for (int j = 0; j < 8; ++j) acc[r][j] = 0.0;
                 // stage c is consumed in iteration c while c+1 and c+2 are in flight; the barrier at the top of an
                 // iteration also says that everybody is done with stage c-1, whose slot stage c+2 is about to overwrite
-                stage(0);
-                if (nchunks > 1) stage(1);
+                if (!RESIDENT) {
+                    stage(0);
+                    if (nchunks > 1) stage(1);
+                }
                 for (int c = 0; c < nchunks; ++c) {
-                    if (c + 1 < nchunks) fb_cp_async_wait<1>();
-                    else fb_cp_async_wait<0>();
-                    __syncthreads();
-                    if (c + 2 < nchunks) stage(c + 2);
+                    if (!RESIDENT) {
+                        if (c + 1 < nchunks) fb_cp_async_wait<1>();
+                        else fb_cp_async_wait<0>();
+                        __syncthreads();
+                        if (c + 2 < nchunks) stage(c + 2);
+                    }
                     if (active) {
-                        const int rows = min(KC, IN - c * KC);
+                        const int rows = RESIDENT ? IN : min(KC, IN - c * KC);
                         const double *ap = Ain + (size_t)c * KC * TM + m0;
-                        const double *wp = wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp + n0;
+                        const double *wp = RESIDENT ? wst + net.woffp[l] + n0 : wst + (size_t)(c % FB_TILE_STAGES) * KC * maxwp + n0;
                         // operands of row k+1 are fetched while row k's multiply-adds issue (two register sets, A / B)
                         double2 xa[2], wa[4], xb[2], wb[4];
 #define FB_TILE_LOAD(X, W, AP, WP)                                                                         \
@@ -251,7 +268,7 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
 #undef FB_TILE_FMA
                     }
                 }
-                __syncthreads();                          // the next round (or layer) restarts the stages
+                if (!RESIDENT) __syncthreads();           // the next round (or layer) restarts the stages
                 if (!active) continue;
                 // bias, ReLU, non-zero counts; hidden activations go to the other buffer
 #pragma unroll
