@@ -295,6 +295,33 @@ def run_gpu(args):
             dist.destroy_process_group()
         return 0
 
+    # side numbers for BASELINE.json's BM-1..8 sweep (full pre-solver + sampled counterexample screen per model on a
+    # window of the stress/BM grid); not part of the headline
+    bm_sweep = {}
+    try:
+        from fairify_b200.domains import STRESS_THRESHOLD
+        z = np.load(os.path.join(ROOT, "tests", "golden", "weights.npz"))
+        DB = DOMAINS["BM"]
+        gb = engine.Grid(DB.columns, DB.ranges, STRESS_THRESHOLD["BM"])
+        nb = min(20000, len(gb))
+        bboxes = gb.boxes(0, nb)
+        blo = [DB.ranges[c][0] for c in DB.columns]; bhi = [DB.ranges[c][1] for c in DB.columns]
+        bpa = DB.columns.index(DB.pa[0])
+        for k in range(1, 9):
+            name = f"BM-{k}"
+            Lk = int(z[f"{name}/L"])
+            mk = engine.Model([z[f"{name}/w{l}"] for l in range(Lk)], [z[f"{name}/b{l}"] for l in range(Lk)])
+            tk = torch.as_tensor(mk.tolerance(blo, bhi)).cuda()
+            for it in range(2):                                   # first pass warms the kernels up
+                b0, b1, b2 = ev(), ev(), ev()
+                b0.record(); mk.prune(bboxes, S=S_SAMPLES, seed=SEED, tol=tk); b1.record()
+                mk.partition_screen(bboxes, bpa, S=S_SAMPLES, seed=SEED); b2.record(); torch.cuda.synchronize()
+            bm_sweep[name] = {"weights": mk.P, "kernels": "specialised" if mk.specialised else "runtime-shape",
+                              "prune_evals_per_s": nb / (b0.elapsed_time(b1) * 1e-3),
+                              "screen_partitions_per_s": nb / (b1.elapsed_time(b2) * 1e-3)}
+    except Exception as exc:                                      # a side measurement must never cost the headline line
+        bm_sweep = {"error": repr(exc)}
+
     P, N = model.P, model.N
     flops_profile = n * S_SAMPLES * (2.0 * P + N)                 # algorithmic FP64 flops of one profile launch
     achieved = flops_profile / (float(prof_ms.item()) * 1e-3) / 1e12
@@ -343,7 +370,8 @@ def run_gpu(args):
         "extra": {"ibp_masks_kernel_ms": ibp_ms, "ibp_only_evals_per_s": n / (ibp_only_ms * 1e-3),
                   "box_generation_boxes_per_s": n / (boxgen_ms * 1e-3),
                   "partition_screen_pairs_per_s": ns * S_SAMPLES / (screen_ms * 1e-3),
-                  "fp64_peak_tflops_measured": peak_tf},
+                  "fp64_peak_tflops_measured": peak_tf,
+                  "bm_sweep_20000_partitions_S1000": bm_sweep},
     }
     print(json.dumps(line), flush=True)
     if world > 1:
