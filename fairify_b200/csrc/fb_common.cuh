@@ -2,11 +2,13 @@
 //
 // Network description comes in two flavours:
 //   * Spec<D0, D1, ..., 1>: layer widths are template constants.  Weights travel as a __grid_constant__
-//     kernel parameter, so every weight is a constant-bank operand of its DFMA/DMUL (no load
-//     instruction at all) and activations / bounds live in registers.  Used for every architecture in
-//     FB_SPEC_LIST (all reference models with at most ~2100 weights).
-//   * GenNet: runtime widths, weights in global memory (staged to shared memory where a kernel reuses
-//     them), activations in local arrays.  Covers everything else (AC-4/5/7, BM-4/7/8, GC-5, unknown nets).
+//     kernel parameter, so every weight reaches its DFMA/DMUL through a uniform register filled from the
+//     constant bank (no global or shared load at all) and activations / bounds live in registers.  Used for
+//     every architecture in the fb_spec_*.cu lists (all reference models whose parameters fit the 32 KB
+//     kernel-parameter space: up to ~3 700 weights).
+//   * GenNet / FbTileNet: runtime widths, weights in global memory (staged to shared memory where a kernel
+//     reuses them).  Covers everything else (AC-4/5, BM-4/7, GC-5, unknown nets): the big ones through tiled,
+//     matrix-product shaped kernels, the small ones with one sample per lane.
 // Both implement exactly the arithmetic of oracle/fairify_oracle.c: term order i ascending, one fused
 // multiply-add per term in the forward passes, separately rounded product and sum in the interval
 // recurrence, bias added last.
