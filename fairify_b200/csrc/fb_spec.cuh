@@ -511,9 +511,12 @@ __device__ __forceinline__ void fb_spec_ibp(const SpecParams<S, double> &prm, co
 }
 
 #define FB_IBP_THREADS 128
+#ifndef FB_IBP_MINB
+#define FB_IBP_MINB 1
+#endif
 
 template <class S>
-__global__ void __launch_bounds__(FB_IBP_THREADS)
+__global__ void __launch_bounds__(FB_IBP_THREADS, FB_IBP_MINB)
 fb_ibp_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n, const int32_t *__restrict__ boxes,
                    const uint32_t *__restrict__ counts, const double *__restrict__ tol,
                    const __grid_constant__ FbPruneOut out)
