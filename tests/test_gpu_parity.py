@@ -242,6 +242,9 @@ assert np.array_equal(r.numpy('ws_ub'), O.ibp(net, hb)[1]) and np.array_equal(r.
 X = O.philox_samples(3, 0, hb, 8).reshape(-1, m.d)
 assert np.array_equal(m.forward(X.astype(np.float64)).cpu().numpy(), O.forward_f64(net, X))
 assert np.array_equal(m.forward(X.astype(np.float32)).cpu().numpy(), O.forward_f32(net, X))
+pa = dom.columns.index(dom.pa[0])
+ce = m.partition_screen(boxes, pa, S=77, seed=3)[0].cpu().numpy()
+assert np.array_equal(ce, O.partition_screen(net, O.philox_samples(3, 0, hb, 77), hb, pa)[0])
 print('generic-ok', m.specialised)
 """
     env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1", FAIRIFY_B200_TILED_PROFILE=tiled)
