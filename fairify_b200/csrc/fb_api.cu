@@ -102,7 +102,7 @@ static bool fb_model_subnormal_free(const GenNet &g, const std::vector<double> &
 static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
 {
     const FbSpecTable *tables[] = {&fb_spec_table_a, &fb_spec_table_b, &fb_spec_table_c, &fb_spec_table_d,
-                                   &fb_spec_table_e, &fb_spec_table_f};
+                                   &fb_spec_table_e, &fb_spec_table_f, &fb_spec_table_g};
     for (const FbSpecTable *t : tables)
         for (int k = 0; k < t->count; ++k) {
             const FbSpecEntry &e = t->entries[k];
@@ -381,7 +381,7 @@ static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const vo
 
 // Runtime-shape profile and partition screen: the tiled kernels (fb_generic.cuh) for the big networks, the sample-per-
 // lane kernels for the rest.  Measured on B200 (% of FP64 peak, tiled vs sample-per-lane profile): BM-4 30 vs 11, AC-4
-// 28 vs 13, AC-5 / BM-7 37 vs 20, GC-5 (a funnel of mostly narrow layers, 4004 weights) 23 vs 21; small networks forced
+// 28 vs 13, AC-5 / BM-7 37 vs 20, a 4004-weight funnel of mostly narrow layers (GC-5's shape) 23 vs 21; small networks forced
 // onto this path lose (AC-1 6 %), hence the weight-count threshold.
 // FAIRIFY_B200_TILED_PROFILE=1 / 0 forces one or the other (tests, comparisons).
 static bool fb_use_tiled_profile(const fb_model *m)
@@ -507,7 +507,10 @@ extern "C" int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const 
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const FbPruneOut *o = reinterpret_cast<const FbPruneOut *>(out);
-    if (fb_use_spec(m)) {
+    // The unrolled one-thread-per-partition kernel holds four bound arrays per layer in registers and spills beyond
+    // ~1200 weights; from there the warp-per-partition runtime-shape kernel is faster (measured on B200, 10^6 boxes:
+    // BM-2 1040 weights 2.2 vs 3.6 ms, AC-2 1400: 8.2 vs 7.4, BM-1 2064: 11.8 vs 5.9, AC-7 3556: 19.7 vs 8.7).
+    if (fb_use_spec(m) && m->gen.P <= 1200) {
         FB_CUDA(m->spec->ibp(m->p64, n, boxes, counts, tol, o, m->num_sms, st));
         return FB_OK;
     }

@@ -7,7 +7,7 @@
 //     every architecture in the fb_spec_*.cu lists (all reference models whose parameters fit the 32 KB
 //     kernel-parameter space: up to ~3 700 weights).
 //   * GenNet / FbTileNet: runtime widths, weights in global memory (staged to shared memory where a kernel
-//     reuses them).  Covers everything else (AC-4/5, BM-4/7, GC-5, unknown nets): the big ones through tiled,
+//     reuses them).  Covers everything else (AC-4/5, BM-4/7, unknown nets): the big ones through tiled,
 //     matrix-product shaped kernels, the small ones with one sample per lane.
 // Both implement exactly the arithmetic of oracle/fairify_oracle.c: term order i ascending, one fused
 // multiply-add per term in the forward passes, separately rounded product and sum in the interval
@@ -129,10 +129,19 @@ struct Spec {
     }
 };
 
-template <class S, typename T>
+// Kernel parameters are limited to 32 764 bytes.  Where float64 weights + float64 biases would not leave room for the
+// other arguments (GC-5: 4004 + 125 values), the biases are kept as the float32 values they are anyway and widened where
+// they are added (exact).
+#define FB_PARAM_BUDGET (32764 - 160)
+template <class S, typename T, bool NARROW_BIAS = (sizeof(T) * (S::P + S::N) > FB_PARAM_BUDGET)>
 struct SpecParams {
     T w[S::P];      // layer-major, element order given by S::widx (filled by fb_spec_fill from the Keras layout)
     T b[S::N];
+};
+template <class S, typename T>
+struct SpecParams<S, T, true> {
+    T w[S::P];
+    float b[S::N];
 };
 
 // host: copy a model given layer-major with [in][out] row-major kernels (what Keras get_weights() returns)
@@ -142,7 +151,7 @@ static inline void fb_spec_fill(SpecParams<S, T> &p, const T *W, const T *B)
     for (int l = 0; l < S::NL; ++l)
         for (int i = 0; i < S::dim(l); ++i)
             for (int j = 0; j < S::dim(l + 1); ++j) p.w[S::widx(l, i, j)] = W[S::woff(l) + i * S::dim(l + 1) + j];
-    for (int k = 0; k < S::N; ++k) p.b[k] = B[k];
+    for (int k = 0; k < S::N; ++k) p.b[k] = static_cast<decltype(p.b[0] + 0)>(B[k]);   // float32-valued either way: exact
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -40,4 +40,5 @@ struct FbSpecTable {
 };
 
 // defined in fb_spec_*.cu
-extern const FbSpecTable fb_spec_table_a, fb_spec_table_b, fb_spec_table_c, fb_spec_table_d, fb_spec_table_e, fb_spec_table_f;
+extern const FbSpecTable fb_spec_table_a, fb_spec_table_b, fb_spec_table_c, fb_spec_table_d, fb_spec_table_e, fb_spec_table_f,
+    fb_spec_table_g;

@@ -22,7 +22,7 @@ template <class S>
 struct FbSpecOps {
     using P64 = SpecParams<S, double>;
     using P32 = SpecParams<S, float>;
-    static_assert(sizeof(P64) + 256 < 32764, "parameter struct exceeds the kernel-parameter limit");
+    static_assert(sizeof(P64) <= FB_PARAM_BUDGET, "parameter struct exceeds the kernel-parameter limit");
 
     static void *make_params64(const double *W, const double *B)
     {
