@@ -453,7 +453,12 @@ static int fb_screen_tiled_launch(const fb_model *m, int64_t n, const int32_t *b
 static int fb_screen_tiled(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
                            int64_t first_index, int pa_col, unsigned long long *key, cudaStream_t st)
 {
-    // 64-row tiles keep two CTAs on an SM (float activations are half the size) and waste less of the last tile
+    // 128-row tiles where two CTAs of that size still share an SM (networks up to 64 wide: BM-7 38 vs 52 ms per 10^5
+    // partitions), 64-row tiles otherwise (BM-4 42 vs 48 ms per 2*10^4, AC-4 90 vs 109 ms per 10^5 with 128)
+    static const int forced_tm = [] { const char *v = getenv("FAIRIFY_B200_SCREEN_TM"); return v ? atoi(v) : 0; }();   // tuning aid
+    const size_t smem128 = fb_screen_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, 128);
+    if (forced_tm != 64 && (smem128 <= 100 * 1024 || (forced_tm == 128 && smem128 <= 220 * 1024)))
+        return fb_screen_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, pa_col, key, st);
     return fb_screen_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, pa_col, key, st);
 }
 

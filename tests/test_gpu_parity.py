@@ -306,7 +306,7 @@ def test_pair_screen_matches_reference_detector(eng, ci):
     assert np.array_equal(np.asarray(pairs, dtype=np.float32).reshape(-1, 2, dom.d), z[f"case{ci}/pairs"])
 
 
-@pytest.mark.parametrize("name", ["AC-1", "AC-3", "GC-1", "GC-4", "BM-5", "AC-5", "BM-4", "AC-4", "GC-5"])
+@pytest.mark.parametrize("name", ["AC-1", "AC-3", "GC-1", "GC-4", "BM-5", "AC-5", "BM-4", "BM-7", "AC-4", "GC-5"])
 def test_partition_screen_matches_oracle(eng, name):
     w, b = G.wb(name)
     m = eng.Model(w, b); net = O.Net(w, b)
