@@ -22,7 +22,8 @@ EXPORTS = [
 class PruneOut(C.Structure):
     """struct fb_prune_out"""
     _fields_ = [(k, C.c_void_p) for k in ("cand", "b_dead", "dead", "sliver", "verdict", "counts",
-                                          "ws_lb", "ws_ub", "pl_lb", "pl_ub", "lb_rd", "ub_ru")]
+                                          "ws_lb", "ws_ub", "pl_lb", "pl_ub", "lb_rd", "ub_ru",
+                                          "s_dead", "s_cand", "record")]
 
 
 class FairifyB200Error(RuntimeError):

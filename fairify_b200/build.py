@@ -41,20 +41,36 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _includes(path, seen=None):
+    """Transitive closure of the quoted #include lines of `path` (repo headers only)."""
+    seen = set() if seen is None else seen
+    here = os.path.dirname(path)
+    with open(path) as f:
+        for line in f:
+            line = line.strip()
+            if line.startswith('#include "'):
+                inc = os.path.normpath(os.path.join(here, line.split('"')[1]))
+                if inc not in seen and os.path.exists(inc):
+                    seen.add(inc)
+                    _includes(inc, seen)
+    return seen
+
+
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    headers = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.h")) + \
-        [os.path.join(HERE, "..", "include", "fairify_b200.h"), os.path.abspath(__file__)]
     sources = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     nvcc = _nvcc()
     jobs = []
-    # the specialisation units include neither the runtime-shape kernels nor the public header
-    spec_headers = [h for h in headers if os.path.basename(h) not in ("fb_generic.cuh", "fairify_b200.h")]
+    wanted = {os.path.basename(s)[:-3] + ".o" for s in sources}
+    for stale in glob.glob(os.path.join(OBJ, "*.o")):              # objects of units that no longer exist
+        if os.path.basename(stale) not in wanted:
+            os.remove(stale)
     for src in sources:
         obj = os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
-        deps = spec_headers if os.path.basename(src).startswith("fb_spec_") else headers
-        if force or _stale(obj, [src] + deps):
+        if force or _stale(obj, [src, os.path.abspath(__file__)] + sorted(_includes(src))):
             jobs.append((src, obj))
+    # the profile units take longest: start them first
+    jobs.sort(key=lambda j: (0 if "fb_specP_" in j[0] else 1, j[0]))
 
     def compile_one(job):
         src, obj = job

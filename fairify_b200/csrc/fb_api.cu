@@ -12,8 +12,8 @@
 
 #include "../../include/fairify_b200.h"
 #include "fb_generic.cuh"
+#include "fb_launch.cuh"
 #include "fb_registry.h"
-#include "fb_spec_ops.cuh"
 
 static_assert(sizeof(fb_prune_out) == sizeof(FbPruneOut), "fb_prune_out and FbPruneOut must match");
 
@@ -41,7 +41,7 @@ static int fb_fail(int code, const char *fmt, ...)
 extern "C" const char *fb_last_error(void) { return fb_err; }
 // for the library's other translation units (not part of the C ABI)
 void fb_set_error(const char *msg) { snprintf(fb_err, sizeof(fb_err), "%s", msg); }
-extern "C" int fb_version(void) { return 100; }
+extern "C" int fb_version(void) { return 200; }
 
 extern "C" int fb_num_sms(int *out)
 {
@@ -62,11 +62,14 @@ struct fb_model {
     std::vector<float> hW32, hB32;
     double *dW64 = nullptr, *dB64 = nullptr;
     float *dW32 = nullptr, *dB32 = nullptr;
-    const FbSpecEntry *spec = nullptr;
+    const FbSpecFwdEntry *spec = nullptr;               // compile-time-specialised kernels for this shape, if any
+    const FbSpecProfileEntry *spec_profile = nullptr;
+    const FbSpecIbpEntry *spec_ibp = nullptr;           // (its launcher is null for shapes left to the runtime-shape kernel)
     void *p64 = nullptr, *p32 = nullptr;
     FbTileNet tile{};               // padded float64 weights for the tiled profile kernel
     double *dWpad = nullptr;
     float *dWpad32 = nullptr;
+    uint32_t *dUnb = nullptr;       // per neuron: a non-zero weight on an input the singular-verification query leaves unbounded
 };
 
 // The specialised profile kernel tests "pre-activation > 0" on the high word of the double, which misreads positive
@@ -99,26 +102,31 @@ static bool fb_model_subnormal_free(const GenNet &g, const std::vector<double> &
     return true;
 }
 
-static const FbSpecEntry *fb_find_spec(int L, const int32_t *dims)
+template <class E, size_t NT>
+static const E *fb_find_spec(const FbSpecTableT<E> *const (&tables)[NT], int L, const int32_t *dims)
 {
-    const FbSpecTable *tables[] = {&fb_spec_table_a, &fb_spec_table_b, &fb_spec_table_c, &fb_spec_table_d,
-                                   &fb_spec_table_e, &fb_spec_table_f, &fb_spec_table_g};
-    for (const FbSpecTable *t : tables)
+    for (const FbSpecTableT<E> *t : tables)
         for (int k = 0; k < t->count; ++k) {
-            const FbSpecEntry &e = t->entries[k];
+            const FbSpecShape &e = t->entries[k].shape;
             if (e.nd != L + 1) continue;
             bool same = true;
             for (int i = 0; i <= L; ++i) same = same && (e.dims[i] == dims[i]);
-            if (same) return &e;
+            if (same) return &t->entries[k];
         }
     return nullptr;
 }
+#define FB_TAB_F(U) &fb_spec_fwd_table_##U,
+#define FB_TAB_P(U) &fb_spec_profile_table_##U,
+#define FB_TAB_I(U) &fb_spec_ibp_table_##U,
+static const FbSpecFwdTable *const fb_fwd_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_F)};
+static const FbSpecProfileTable *const fb_profile_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_P)};
+static const FbSpecIbpTable *const fb_ibp_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_I)};
 
 extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32); cudaFree(m->dUnb);
     delete m;
 }
 
@@ -169,6 +177,22 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
     }
     g.W64 = m->dW64; g.B64 = m->dB64; g.W32 = m->dW32; g.B32 = m->dB32;
     {
+        // singular_verification* bounds only the first out_l inputs of a hidden layer l >= 1 (utils/prune.py:266-273 with
+        // :302-345); a neuron with a non-zero weight on any later input can always be made positive (see fb_spec.cuh)
+        std::vector<uint32_t> unb((size_t)(g.N + 31) / 32, 0u);
+        for (int l = 1; l + 1 < L; ++l)
+            for (int j = 0; j < dims[l + 1]; ++j)
+                for (int k = dims[l + 1]; k < dims[l]; ++k)
+                    if (m->hW64[(size_t)g.woff[l] + (size_t)k * dims[l + 1] + j] != 0.0) {
+                        unb[(g.boff[l] + j) >> 5] |= 1u << ((g.boff[l] + j) & 31);
+                        break;
+                    }
+        e = cudaMalloc(&m->dUnb, sizeof(uint32_t) * unb.size());
+        if (e == cudaSuccess) e = cudaMemcpy(m->dUnb, unb.data(), sizeof(uint32_t) * unb.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
+        g.unb = m->dUnb;
+    }
+    {
         // weights with every row padded to a multiple of 32 columns (zeros): operand of fb_profile_tile_kernel
         FbTileNet &t = m->tile;
         t.L = L; t.N = g.N; t.maxw = g.maxw;
@@ -191,7 +215,10 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
         t.Wp = m->dWpad; t.B = m->dB64; t.Wp32 = m->dWpad32; t.B32 = m->dB32;
     }
-    m->spec = fb_find_spec(L, dims);
+    m->spec = fb_find_spec(fb_fwd_tables, L, dims);
+    m->spec_profile = fb_find_spec(fb_profile_tables, L, dims);
+    m->spec_ibp = fb_find_spec(fb_ibp_tables, L, dims);
+    if (!m->spec_profile || !m->spec_ibp) m->spec = nullptr;
     if (m->spec && !fb_model_subnormal_free(g, m->hW64, m->hB64)) m->spec = nullptr;   // runtime-shape kernels: exact sign test
     if (m->spec) {
         m->p64 = m->spec->make_params64(m->hW64.data(), m->hB64.data());
@@ -478,7 +505,7 @@ extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, co
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
     if (chunks > 1) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));
     if (fb_use_spec(m)) {
-        FB_CUDA(m->spec->profile(m->p64, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks, chunk_len,
+        FB_CUDA(m->spec_profile->profile(m->p64, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks, chunk_len,
                                  counts, m->num_sms, st));
         return FB_OK;
     }
@@ -512,11 +539,9 @@ extern "C" int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const 
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const FbPruneOut *o = reinterpret_cast<const FbPruneOut *>(out);
-    // The unrolled one-thread-per-partition kernel holds four bound arrays per layer in registers and spills beyond
-    // ~1200 weights; from there the warp-per-partition runtime-shape kernel is faster (measured on B200, 10^6 boxes:
-    // BM-2 1040 weights 2.2 vs 3.6 ms, AC-2 1400: 8.2 vs 7.4, BM-1 2064: 11.8 vs 5.9, AC-7 3556: 19.7 vs 8.7).
-    if (fb_use_spec(m) && m->gen.P <= 1200) {
-        FB_CUDA(m->spec->ibp(m->p64, n, boxes, counts, tol, o, m->num_sms, st));
+    // (shapes above ~1200 weights have no specialised bounds kernel: fb_spec_ops_ibp.cuh)
+    if (fb_use_spec(m) && m->spec_ibp->ibp != nullptr) {
+        FB_CUDA(m->spec_ibp->ibp(m->p64, n, boxes, counts, tol, m->dUnb, o, m->num_sms, st));
         return FB_OK;
     }
     auto k = fb_ibp_gen_kernel;
@@ -603,6 +628,8 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
         {out->ws_lb, fb, (void **)&dev.ws_lb, nullptr},   {out->ws_ub, fb, (void **)&dev.ws_ub, nullptr},
         {out->pl_lb, fb, (void **)&dev.pl_lb, nullptr},   {out->pl_ub, fb, (void **)&dev.pl_ub, nullptr},
         {out->lb_rd, fb, (void **)&dev.lb_rd, nullptr},   {out->ub_ru, fb, (void **)&dev.ub_ru, nullptr},
+        {out->s_dead, mb, (void **)&dev.s_dead, nullptr}, {out->s_cand, mb, (void **)&dev.s_cand, nullptr},
+        {out->record, sizeof(uint32_t) * (2 * NW + 2), (void **)&dev.record, nullptr},
     };
     std::vector<DevBuf> bufs;
     bufs.reserve(sizeof(slots) / sizeof(slots[0]));

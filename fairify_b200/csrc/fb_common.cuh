@@ -132,7 +132,7 @@ struct Spec {
 // Kernel parameters are limited to 32 764 bytes.  Where float64 weights + float64 biases would not leave room for the
 // other arguments (GC-5: 4004 + 125 values), the biases are kept as the float32 values they are anyway and widened where
 // they are added (exact).
-#define FB_PARAM_BUDGET (32764 - 160)
+#define FB_PARAM_BUDGET (32764 - 224)
 template <class S, typename T, bool NARROW_BIAS = (sizeof(T) * (S::P + S::N) > FB_PARAM_BUDGET)>
 struct SpecParams {
     T w[S::P];      // layer-major, element order given by S::widx (filled by fb_spec_fill from the Keras layout)
@@ -164,6 +164,7 @@ struct GenNet {
     int boff[FB_MAX_LAYERS + 1];
     const double *W64, *B64;
     const float *W32, *B32;
+    const uint32_t *unb;      // [NW] neuron has a non-zero weight on an input its singular-verification query leaves unbounded
 };
 
 // ---------------------------------------------------------------------------------------------------

@@ -567,15 +567,18 @@ fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes
                   const double *__restrict__ tol, const FbPruneOut o)
 {
     __shared__ double sb[FB_IBP_GEN_WARPS][8][FB_MAXW];      // lb, ub, lbd, ubd  x  {in, out}
-    __shared__ uint32_t sm[FB_IBP_GEN_WARPS][3][FB_MAX_NW];
+    __shared__ uint32_t sm[FB_IBP_GEN_WARPS][7][FB_MAX_NW];  // cand, b_dead, sliver, b_cand, s_dead, s_cand, dead
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int N = net.N, NW = (N + 31) / 32, D0 = net.dims[0];
     const int64_t nwarps = (int64_t)gridDim.x * FB_IBP_GEN_WARPS;
     for (int64_t p = (int64_t)blockIdx.x * FB_IBP_GEN_WARPS + wib; p < n; p += nwarps) {
         double *lb = sb[wib][0], *ub = sb[wib][1], *lbd = sb[wib][2], *ubd = sb[wib][3];
         double *nlb = sb[wib][4], *nub = sb[wib][5], *nlbd = sb[wib][6], *nubd = sb[wib][7];
-        uint32_t *cand_w = sm[wib][0], *bdead_w = sm[wib][1], *sliver_w = sm[wib][2];
-        for (int k = lane; k < NW; k += 32) { cand_w[k] = 0; bdead_w[k] = 0; sliver_w[k] = 0; }
+        uint32_t *cand_w = sm[wib][0], *bdead_w = sm[wib][1], *sliver_w = sm[wib][2], *bcand_w = sm[wib][3];
+        uint32_t *sdead_w = sm[wib][4], *scand_w = sm[wib][5], *dead_w = sm[wib][6];
+        for (int k = lane; k < NW; k += 32) {
+            cand_w[k] = 0; bdead_w[k] = 0; sliver_w[k] = 0; bcand_w[k] = 0; sdead_w[k] = 0; scand_w[k] = 0; dead_w[k] = 0;
+        }
         for (int i = lane; i < D0; i += 32) {
             const int lo = __ldg(boxes + p * (2 * D0) + 2 * i), hi = __ldg(boxes + p * (2 * D0) + 2 * i + 1);
             lb[i] = lbd[i] = (double)lo; ub[i] = ubd[i] = (double)hi;
@@ -586,11 +589,12 @@ fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes
             const int IN = net.dims[l], OUT = net.dims[l + 1], BO = net.boff[l];
             const double *w = net.W64 + net.woff[l];
             const bool last = (l == net.L - 1);
-            bool all1 = true;
+            const uint32_t first = 1u << (BO & 31);
+            bool all1 = true, anyc = false;
             for (int jb = 0; jb < OUT; jb += 32) {
                 const int j = jb + lane;
                 const bool live = j < OUT;
-                bool bd = true;
+                bool bd = true, bc = false;
                 if (live) {
                     double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
                     for (int i = 0; i < IN; ++i) {
@@ -612,8 +616,10 @@ fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes
                     const uint32_t bit = 1u << (idx & 31);
                     if (c) atomicOr(&cand_w[idx >> 5], bit);
                     bd = last ? c : (c && le0);
+                    bc = last ? c : (c && !le0);
                     if (bd) atomicOr(&bdead_w[idx >> 5], bit);
-                    if (!last && tol != nullptr && c && !le0 && wu <= tol[idx]) atomicOr(&sliver_w[idx >> 5], bit);
+                    if (bc) atomicOr(&bcand_w[idx >> 5], bit);
+                    if (l == 0 && !last && tol != nullptr && bc && wu <= tol[idx]) atomicOr(&sliver_w[idx >> 5], bit);
                     if (last) { out_lbd = wld; out_ubd = wud; }
                     if (o.counts16) o.counts16[p * N + idx] = (uint16_t)c32;
                     if (o.ws_lb) o.ws_lb[p * N + idx] = wl;
@@ -626,9 +632,55 @@ fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes
                     nlbd[j] = wld < 0.0 ? 0.0 : wld; nubd[j] = wud < 0.0 ? 0.0 : wud;
                 }
                 all1 = __all_sync(0xffffffffu, !live || bd) && all1;
+                anyc = __any_sync(0xffffffffu, live && bc) || anyc;
             }
             __syncwarp();
-            if (all1 && lane == 0) bdead_w[BO >> 5] &= ~(1u << (BO & 31));        // keep-one fix
+            // singular verification in closed form (see FbIbpSink in fb_spec.cuh): hidden layers l >= 1, candidates the
+            // bound did not settle; the inputs are this layer's own post-activation bounds nlb / nub
+            bool sall1 = last;                                  // last layer: s_dead is the copied b_cand, then keep-one
+            if (!last && l >= 1 && anyc) {
+                const int MM = min(IN, OUT);
+                sall1 = true;
+                for (int jb = 0; jb < OUT; jb += 32) {
+                    const int j = jb + lane, idx = BO + j;
+                    const bool live = j < OUT;
+                    bool sd = false;
+                    if (live && ((bcand_w[idx >> 5] >> (idx & 31)) & 1u) && !((__ldg(net.unb + (idx >> 5)) >> (idx & 31)) & 1u)) {
+                        double q = 0.0;
+                        for (int k = 0; k < MM; ++k) {
+                            const double wt = __ldg(w + (int64_t)k * OUT + j);
+                            q = __dadd_rn(q, __dmul_rn(wt, fb_signbit(wt) ? nlb[k] : nub[k]));
+                        }
+                        q = __dadd_rn(q, __ldg(net.B64 + idx));
+                        sd = q <= 0.0;
+                        if (sd) atomicOr(&sdead_w[idx >> 5], 1u << (idx & 31));
+                        if (tol != nullptr && fabs(q) <= tol[idx]) atomicOr(&sliver_w[idx >> 5], 1u << (idx & 31));
+                    }
+                    sall1 = __all_sync(0xffffffffu, !live || sd) && sall1;
+                }
+                __syncwarp();
+            }
+            // s_cand = b_cand minus what the query found; keep-one fixes on b_dead, s_dead and their union
+            bool dall1 = true;
+            for (int jb = 0; jb < OUT; jb += 32) {
+                const int j = jb + lane, idx = BO + j;
+                bool dd = true;
+                if (j < OUT) {
+                    const uint32_t bit = 1u << (idx & 31);
+                    const bool bcb = bcand_w[idx >> 5] & bit, sdb = sdead_w[idx >> 5] & bit;
+                    if (bcb && !sdb) atomicOr(&scand_w[idx >> 5], bit);
+                    const bool clear_b = all1 && j == 0, clear_s = sall1 && j == 0;
+                    dd = ((bdead_w[idx >> 5] & bit) && !clear_b) || (sdb && !clear_s);
+                    if (dd) atomicOr(&dead_w[idx >> 5], bit);
+                }
+                dall1 = __all_sync(0xffffffffu, dd) && dall1;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                if (all1) bdead_w[BO >> 5] &= ~first;
+                if (sall1) sdead_w[BO >> 5] &= ~first;
+                if (dall1) dead_w[BO >> 5] &= ~first;
+            }
             double *t;
             t = lb; lb = nlb; nlb = t; t = ub; ub = nub; nub = t;
             t = lbd; lbd = nlbd; nlbd = t; t = ubd; ubd = nubd; nubd = t;
@@ -641,16 +693,20 @@ fb_ibp_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes
         for (int k = lane; k < NW; k += 32) {
             if (o.cand) o.cand[p * NW + k] = cand_w[k];
             if (o.b_dead) o.b_dead[p * NW + k] = bdead_w[k];
-            if (o.dead) o.dead[p * NW + k] = bdead_w[k];
+            if (o.dead) o.dead[p * NW + k] = dead_w[k];
             if (o.sliver) o.sliver[p * NW + k] = sliver_w[k];
+            if (o.s_dead) o.s_dead[p * NW + k] = sdead_w[k];
+            if (o.s_cand) o.s_cand[p * NW + k] = scand_w[k];
+            if (o.record) { o.record[p * (2 * NW + 2) + 1 + k] = dead_w[k]; o.record[p * (2 * NW + 2) + 1 + NW + k] = cand_w[k]; }
             anysl |= sliver_w[k];
         }
         anysl = __reduce_or_sync(0xffffffffu, anysl);
-        if (lane == 0 && o.verdict) {
+        if (lane == 0) {
             uint8_t v = 0;
             if (out_lbd > 0.0 || out_ubd < 0.0) v |= FB_VERDICT_CERTIFIED;
             if (anysl) v |= FB_VERDICT_SLIVER;
-            o.verdict[p] = v;
+            if (o.verdict) o.verdict[p] = v;
+            if (o.record) { o.record[p * (2 * NW + 2)] = v; o.record[p * (2 * NW + 2) + 1 + 2 * NW] = 0xffffffffu; }
         }
         __syncwarp();
     }

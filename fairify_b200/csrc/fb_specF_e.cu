@@ -1,0 +1,5 @@
+// fwd kernels of the architectures in FB_SPEC_LIST_e (fb_spec_lists.h)
+#include "fb_spec_ops_fwd.cuh"
+#include "fb_spec_lists.h"
+static const FbSpecFwdEntry entries[] = {FB_SPEC_LIST_e(FB_SPEC_FWD_ENTRY)};
+const FbSpecFwdTable fb_spec_fwd_table_e = {entries, (int)(sizeof(entries) / sizeof(entries[0]))};

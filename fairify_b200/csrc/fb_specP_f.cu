@@ -1,0 +1,5 @@
+// profile kernels of the architectures in FB_SPEC_LIST_f (fb_spec_lists.h)
+#include "fb_spec_ops_profile.cuh"
+#include "fb_spec_lists.h"
+static const FbSpecProfileEntry entries[] = {FB_SPEC_LIST_f(FB_SPEC_PROFILE_ENTRY)};
+const FbSpecProfileTable fb_spec_profile_table_f = {entries, (int)(sizeof(entries) / sizeof(entries[0]))};

@@ -1,0 +1,241 @@
+// fb_spec_ibp.cuh -- compile-time-specialised interval recurrence + mask algebra (see fb_common.cuh): per box
+// 8P + 4N directed/nearest DMUL/DADD, weights as immediate constant-bank operands, bounds in registers.
+#pragma once
+#include "fb_common.cuh"
+
+// ---------------------------------------------------------------------------------------------------
+// interval recurrence + mask algebra, one partition per thread.
+// reference: neuron_bounds utils/prune.py:105-164 (round-to-nearest chain, separately rounded product
+// and sum), dead_node_from_bound :226-251, keep-one fix :689-691, merge :941-948.  The second chain
+// rounds outward (lower bound toward -inf, upper toward +inf) and is what the verdict and the reported
+// enclosure use.
+// ---------------------------------------------------------------------------------------------------
+struct FbPruneOut {
+    uint32_t *cand;       // [n][NW]  count == 0
+    uint32_t *b_dead;     // [n][NW]  cand & (ws_ub <= 0), keep-one applied
+    uint32_t *dead;       // [n][NW]  b_dead | s_dead, keep-one applied
+    uint32_t *sliver;     // [n][NW]  neurons whose s_dead is within rounding error: the host Z3 query decides
+    uint8_t *verdict;     // [n]
+    uint16_t *counts16;   // [n][N]   non-zero activation counts (pos_prob * S)
+    double *ws_lb, *ws_ub, *pl_lb, *pl_ub;   // [n][N]  round-to-nearest, reference-exact
+    double *lb_rd, *ub_ru;                   // [n][N]  outward rounded
+    uint32_t *s_dead;     // [n][NW]  singular verification in closed form (fb_singular below), keep-one applied
+    uint32_t *s_cand;     // [n][NW]  b_cand minus the neurons s_dead found (before its keep-one fix)
+    uint32_t *record;     // [n][2*NW+2]  verdict | dead[NW] | cand[NW] | first-counterexample sample (-1 here)
+};
+
+// singular_verification* (utils/prune.py:276-644) in closed form.  For a still-candidate neuron j of hidden layer
+// l >= 1 the reference asks Z3 whether  y_j = sum_k w_kj x_k + b_j > 0  can hold with x_k boxed by
+// pl_lb[l][k] <= x_k <= pl_ub[l][k] for k < out_l -- intermediate_domain_constraint (:266-273) is called with the
+// layer's OWN index (:302-345), so the bounds are the post-activation bounds of layer l itself, index for index, and the
+// inputs k >= out_l are unconstrained Reals.  The query is sat iff an unconstrained input has a non-zero weight (`unb`,
+// a per-model bit computed by fb_model_create) or
+//     q_j = sum_{k < min(in_l, out_l)} max(w_kj pl_lb[l][k], w_kj pl_ub[l][k]) + b_j > 0,
+// so s_dead = b_cand & !unb & (q <= 0).  q is evaluated k ascending with separately rounded product and sum, bias last
+// (same as the oracle's singular_one); |q| <= tol flags the neuron for the host's exact Z3 query.  On layer 0 the
+// variables are the integer box itself and q is ws_ub, which is > 0 for every b_cand neuron: only the flag remains.
+template <class S>
+struct FbIbpSink {
+    static constexpr int N = S::N, NW = S::NW;
+    const uint32_t *cnt;      // this partition's counts or nullptr (then every neuron is a candidate)
+    const double *tol;        // [N] or nullptr
+    const uint32_t *unb;      // [NW] per-model: neuron has a non-zero weight on an input the query leaves unbounded
+    const FbPruneOut &o;
+    int64_t p;
+    uint32_t cand_w[NW], bdead_w[NW], sliver_w[NW], bcand_w[NW], sdead_w[NW], scand_w[NW], dead_w[NW];
+    double out_lb_rd, out_ub_ru;
+
+    __device__ __forceinline__ FbIbpSink(const FbPruneOut &o_, int64_t p_, const uint32_t *cnt_, const double *tol_,
+                                         const uint32_t *unb_)
+        : cnt(cnt_), tol(tol_), unb(unb_), o(o_), p(p_)
+    {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            cand_w[k] = 0; bdead_w[k] = 0; sliver_w[k] = 0; bcand_w[k] = 0; sdead_w[k] = 0; scand_w[k] = 0; dead_w[k] = 0;
+        }
+    }
+
+    // idx / last / first are compile-time constants after unrolling (the call sits in fully unrolled loops)
+    __device__ __forceinline__ void neuron(int idx, bool last, bool first, double lb, double ub, double lbd, double ubd)
+    {
+        uint32_t c32 = 0;
+        if (cnt) c32 = cnt[idx];
+        const bool c = c32 == 0;
+        const bool le0 = ub <= 0.0;
+        const uint32_t bit = 1u << (idx & 31);
+        if (c) cand_w[idx >> 5] |= bit;
+        if (last) { if (c) { bdead_w[idx >> 5] |= bit; bcand_w[idx >> 5] |= bit; } out_lb_rd = lbd; out_ub_ru = ubd; }
+        else {
+            if (c && le0) bdead_w[idx >> 5] |= bit;
+            if (c && !le0) bcand_w[idx >> 5] |= bit;
+            if (first && tol != nullptr && c && !le0 && ub <= tol[idx]) sliver_w[idx >> 5] |= bit;
+        }
+        if (o.counts16) o.counts16[p * N + idx] = (uint16_t)c32;
+        if (o.ws_lb) o.ws_lb[p * N + idx] = lb;
+        if (o.ws_ub) o.ws_ub[p * N + idx] = ub;
+        if (o.pl_lb) o.pl_lb[p * N + idx] = lb < 0.0 ? 0.0 : lb;
+        if (o.pl_ub) o.pl_ub[p * N + idx] = ub < 0.0 ? 0.0 : ub;
+        if (o.lb_rd) o.lb_rd[p * N + idx] = lbd;
+        if (o.ub_ru) o.ub_ru[p * N + idx] = ubd;
+    }
+
+    __device__ __forceinline__ bool is_bcand(int idx) const { return (bcand_w[idx >> 5] >> (idx & 31)) & 1u; }
+
+    // the closed-form query result of a b_cand neuron of a hidden layer l >= 1
+    __device__ __forceinline__ void singular(int idx, double q)
+    {
+        const uint32_t bit = 1u << (idx & 31);
+        if ((__ldg(unb + (idx >> 5)) & bit) != 0u) return;                  // sat whatever the bounds
+        if (q <= 0.0) sdead_w[idx >> 5] |= bit;
+        if (tol != nullptr && fabs(q) <= tol[idx]) sliver_w[idx >> 5] |= bit;
+    }
+
+    // all bits [BO, BO+OUT) of w set?
+    template <int BO, int OUT>
+    __device__ __forceinline__ bool all_set(const uint32_t (&w)[NW]) const
+    {
+        bool all1 = true;
+#pragma unroll
+        for (int k = BO >> 5; k <= (BO + OUT - 1) >> 5; ++k) {
+            const int b0 = (k * 32 > BO) ? k * 32 : BO;
+            const int b1 = ((k + 1) * 32 < BO + OUT) ? (k + 1) * 32 : BO + OUT;
+            const uint32_t m = (b1 - b0 == 32) ? 0xffffffffu : (((1u << (b1 - b0)) - 1u) << (b0 & 31));
+            all1 = all1 && ((w[k] & m) == m);
+        }
+        return all1;
+    }
+
+    // end of the layer occupying bits [BO, BO+OUT): s_cand, then the keep-one fixes (utils/prune.py:689-691, :698-700,
+    // :703-705: a mask with no 0 in a layer gets its first entry cleared) on b_dead, s_dead and their union
+    template <int BO, int OUT, bool LAST>
+    __device__ __forceinline__ void layer_done()
+    {
+        constexpr uint32_t first = 1u << (BO & 31);
+#pragma unroll
+        for (int k = BO >> 5; k <= (BO + OUT - 1) >> 5; ++k) {
+            const int b0 = (k * 32 > BO) ? k * 32 : BO;
+            const int b1 = ((k + 1) * 32 < BO + OUT) ? (k + 1) * 32 : BO + OUT;
+            const uint32_t m = (b1 - b0 == 32) ? 0xffffffffu : (((1u << (b1 - b0)) - 1u) << (b0 & 31));
+            scand_w[k] |= bcand_w[k] & ~sdead_w[k] & m;
+        }
+        if (LAST) sdead_w[BO >> 5] |= bcand_w[BO >> 5] & first;               // copied through (:287-288), cleared below
+        if (all_set<BO, OUT>(bdead_w)) bdead_w[BO >> 5] &= ~first;
+        if (all_set<BO, OUT>(sdead_w)) sdead_w[BO >> 5] &= ~first;
+#pragma unroll
+        for (int k = BO >> 5; k <= (BO + OUT - 1) >> 5; ++k) {
+            const int b0 = (k * 32 > BO) ? k * 32 : BO;
+            const int b1 = ((k + 1) * 32 < BO + OUT) ? (k + 1) * 32 : BO + OUT;
+            const uint32_t m = (b1 - b0 == 32) ? 0xffffffffu : (((1u << (b1 - b0)) - 1u) << (b0 & 31));
+            dead_w[k] |= (bdead_w[k] | sdead_w[k]) & m;
+        }
+        if (all_set<BO, OUT>(dead_w)) dead_w[BO >> 5] &= ~first;
+    }
+
+    __device__ __forceinline__ void finish()
+    {
+        uint32_t anysl = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (o.cand) o.cand[p * NW + k] = cand_w[k];
+            if (o.b_dead) o.b_dead[p * NW + k] = bdead_w[k];
+            if (o.dead) o.dead[p * NW + k] = dead_w[k];
+            if (o.sliver) o.sliver[p * NW + k] = sliver_w[k];
+            if (o.s_dead) o.s_dead[p * NW + k] = sdead_w[k];
+            if (o.s_cand) o.s_cand[p * NW + k] = scand_w[k];
+            anysl |= sliver_w[k];
+        }
+        uint8_t v = 0;
+        if (out_lb_rd > 0.0 || out_ub_ru < 0.0) v |= FB_VERDICT_CERTIFIED;
+        if (anysl) v |= FB_VERDICT_SLIVER;
+        if (o.verdict) o.verdict[p] = v;
+        if (o.record) {
+            uint32_t *r = o.record + p * (2 * NW + 2);
+            r[0] = v;
+#pragma unroll
+            for (int k = 0; k < NW; ++k) { r[1 + k] = dead_w[k]; r[1 + NW + k] = cand_w[k]; }
+            r[1 + 2 * NW] = 0xffffffffu;
+        }
+    }
+};
+
+template <class S, int l>
+__device__ __forceinline__ void fb_spec_ibp(const SpecParams<S, double> &prm, const double (&lb)[S::dim(l)],
+                                            const double (&ub)[S::dim(l)], const double (&lbd)[S::dim(l)],
+                                            const double (&ubd)[S::dim(l)], FbIbpSink<S> &sink)
+{
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), BO = S::boff(l);
+    constexpr bool last = (l == S::NL - 1);
+    double nlb[OUT], nub[OUT], nlbd[OUT], nubd[OUT];
+#pragma unroll
+    for (int j = 0; j < OUT; ++j) {
+        double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+            const double w = prm.w[S::widx(l, i, j)];
+            const bool neg = fb_signbit(w);            // host canonicalises -0.0 to +0.0
+            const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+            const double ad = neg ? ubd[i] : lbd[i], bd = neg ? lbd[i] : ubd[i];
+            mn = __dadd_rn(mn, __dmul_rn(w, a));
+            mx = __dadd_rn(mx, __dmul_rn(w, b));
+            mnd = __dadd_rd(mnd, __dmul_rd(w, ad));
+            mxd = __dadd_ru(mxd, __dmul_ru(w, bd));
+        }
+        const double bj = prm.b[BO + j];
+        const double wl = __dadd_rn(mn, bj), wu = __dadd_rn(mx, bj);
+        const double wld = __dadd_rd(mnd, bj), wud = __dadd_ru(mxd, bj);
+        sink.neuron(BO + j, last, l == 0, wl, wu, wld, wud);
+        nlb[j] = wl < 0.0 ? 0.0 : wl; nub[j] = wu < 0.0 ? 0.0 : wu;
+        nlbd[j] = wld < 0.0 ? 0.0 : wld; nubd[j] = wud < 0.0 ? 0.0 : wud;
+    }
+    if constexpr (l >= 1 && !last) {
+        // singular verification of this layer's remaining candidates (rare: most boxes have none left here)
+        constexpr int MM = IN < OUT ? IN : OUT;
+        uint32_t any = 0;
+#pragma unroll
+        for (int k = BO >> 5; k <= (BO + OUT - 1) >> 5; ++k) any |= sink.bcand_w[k];     // (earlier layers' bits are 0 here
+        if (any) {                                                                       //  only if they had no candidate: harmless)
+#pragma unroll
+            for (int j = 0; j < OUT; ++j) {
+                if (sink.is_bcand(BO + j)) {
+                    double q = 0.0;
+#pragma unroll
+                    for (int k = 0; k < MM; ++k) {
+                        const double w = prm.w[S::widx(l, k, j)];
+                        q = __dadd_rn(q, __dmul_rn(w, fb_signbit(w) ? nlb[k] : nub[k]));
+                    }
+                    sink.singular(BO + j, __dadd_rn(q, (double)prm.b[BO + j]));
+                }
+            }
+        }
+    }
+    sink.template layer_done<BO, OUT, last>();
+    if constexpr (!last) fb_spec_ibp<S, l + 1>(prm, nlb, nub, nlbd, nubd, sink);
+}
+
+#define FB_IBP_THREADS 128
+#ifndef FB_IBP_MINB
+#define FB_IBP_MINB 1
+#endif
+
+template <class S>
+__global__ void __launch_bounds__(FB_IBP_THREADS, FB_IBP_MINB)
+fb_ibp_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n, const int32_t *__restrict__ boxes,
+                   const uint32_t *__restrict__ counts, const double *__restrict__ tol,
+                   const uint32_t *__restrict__ unb, const __grid_constant__ FbPruneOut out)
+{
+    constexpr int D0 = S::D0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        double lb[D0], ub[D0];
+        const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+#pragma unroll
+        for (int i = 0; i < D0; ++i) {
+            const int2 b = __ldg(bx + i);
+            lb[i] = (double)b.x; ub[i] = (double)b.y;
+        }
+        FbIbpSink<S> sink(out, p, counts ? counts + p * S::N : nullptr, tol, unb);
+        fb_spec_ibp<S, 0>(prm, lb, ub, lb, ub, sink);
+        sink.finish();
+    }
+}
+

@@ -22,10 +22,10 @@ import torch
 from . import _lib
 from ._lib import FairifyB200Error, PruneOut, check
 
-MASK_OUTPUTS = ("cand", "b_dead", "dead", "sliver")
+MASK_OUTPUTS = ("cand", "b_dead", "dead", "sliver", "s_dead", "s_cand")
 BOUND_OUTPUTS = ("ws_lb", "ws_ub", "pl_lb", "pl_ub", "lb_rd", "ub_ru")
 DEFAULT_OUTPUTS = ("cand", "b_dead", "dead", "sliver", "verdict", "counts")
-ALL_OUTPUTS = DEFAULT_OUTPUTS + BOUND_OUTPUTS
+ALL_OUTPUTS = DEFAULT_OUTPUTS + BOUND_OUTPUTS + ("s_dead", "s_cand", "record")
 
 VERDICT_CERTIFIED, VERDICT_CE, VERDICT_SLIVER = 1, 2, 4
 
@@ -61,19 +61,27 @@ def pack_bits(bits):
 
 
 def sliver_tolerance(w, b, lo, hi):
-    """Per-neuron bound on |float ws_ub - exact ws_ub| valid for every box inside [lo, hi].
+    """Per-neuron tolerance below which the float sign of the singular-verification quantity is not trusted, valid
+    for every box inside [lo, hi] (argument `tol` of fb_ibp / fb_prune).
 
-    (in+2) roundings of relative size 2^-53 on terms whose magnitudes sum to at most
-    M_j = sum_i |w_ij| max|x_i| + |b_j|, times a safety factor of 4.  A candidate neuron with
-    0 < ws_ub <= tol is a "sliver": only there can the reference's Z3 query
-    (singular_verification, utils/prune.py:276-356) disagree with the sign of the float bound.
+    The reference's Z3 query (singular_verification*, utils/prune.py:276-644) decides the sign of an exact sum; the
+    device evaluates the same sum in float64.  Layer 0: the sum is ws_ub -- (in+2) roundings of relative size 2^-53 on
+    terms whose magnitudes add up to at most M_j = sum_i |w_ij| max|x_i| + |b_j|.  Layer l >= 1: the sum is q_j, over
+    the first min(in, out) inputs boxed by the layer's OWN post-activation bounds (see include/fairify_b200.h, fb_ibp),
+    whose magnitudes are at most M_l, so its terms add up to at most sum_k |w_kj| M_l[k] + |b_j|; Z3 also reads every
+    float through its decimal repr, one more relative 2^-53 per factor.  Both with a safety factor of 4.  A candidate
+    whose |sum| is within the tolerance is a "sliver": the host puts the reference's own query to Z3 for it.
     """
     mag = np.maximum(np.abs(np.asarray(lo, dtype=np.float64)), np.abs(np.asarray(hi, dtype=np.float64)))
     out = []
-    for wl, bl in zip(w, b):
+    for l, (wl, bl) in enumerate(zip(w, b)):
         wl = np.abs(np.asarray(wl, dtype=np.float64)); bl = np.abs(np.asarray(bl, dtype=np.float64))
         M = mag @ wl + bl
-        out.append(4.0 * (wl.shape[0] + 2) * 2.0 ** -53 * M)
+        if l == 0:
+            out.append(4.0 * (wl.shape[0] + 2) * 2.0 ** -53 * M)
+        else:
+            mm = min(wl.shape)
+            out.append(4.0 * (mm + 4) * 2.0 ** -53 * (M[:mm] @ wl[:mm] + bl))
         mag = M
     return np.concatenate(out)
 
@@ -165,6 +173,8 @@ class Model:
                 t[k] = torch.empty((n, self.N), dtype=torch.int16, device=self.device)
             elif k in BOUND_OUTPUTS:
                 t[k] = torch.empty((n, self.N), dtype=torch.float64, device=self.device)
+            elif k == "record":
+                t[k] = torch.empty((n, 2 * self.NW + 2), dtype=torch.int32, device=self.device)
             else:
                 raise ValueError(f"unknown output {k!r}")
         po = PruneOut()
@@ -239,6 +249,8 @@ class Model:
                 shapes[k] = ((n,), torch.uint8)
             elif k == "counts":
                 shapes[k] = ((n, self.N), torch.int16)
+            elif k == "record":
+                shapes[k] = ((n, 2 * self.NW + 2), torch.int32)
             else:
                 shapes[k] = ((n, self.N), torch.float64)
         return {k: torch.empty(s, dtype=dt).pin_memory() for k, (s, dt) in shapes.items()}

@@ -49,12 +49,17 @@ typedef struct fb_grid fb_grid;
 typedef struct fb_prune_out {
     uint32_t *cand;     /* candidates: never active on the samples      (candidate_dead_nodes, utils/prune.py:183-187) */
     uint32_t *b_dead;   /* b_dead_node_mask after the keep-one fix       (dead_node_from_bound :226-251, :689-691)     */
-    uint32_t *dead;     /* dead_nodes = merge(b_dead, s_dead) + keep-one (:702-705); s_dead is 0 unless `sliver`       */
-    uint32_t *sliver;   /* neurons the host must hand to singular_verification (:276-356)                              */
+    uint32_t *dead;     /* dead_nodes = merge(b_dead, s_dead) + keep-one (:702-705)                                    */
+    uint32_t *sliver;   /* neurons whose s_dead the float arithmetic cannot decide: hand them to the Z3 query (:276-356) */
     uint8_t *verdict;   /* [n] FB_VERDICT_* bits                                                                       */
     uint16_t *counts;   /* [n][N] non-zero activation counts; pos_prob = counts / S (:188-191)                         */
     double *ws_lb, *ws_ub, *pl_lb, *pl_ub; /* [n][N] neuron_bounds, round-to-nearest, reference-exact (:105-164)      */
     double *lb_rd, *ub_ru;                 /* [n][N] outward-rounded enclosure of the same recurrence                  */
+    uint32_t *s_dead;   /* s_dead_node_mask of singular_verification* (:276-644) after the keep-one fix (:698-700), from
+                         * the closed form of the query the reference gives Z3 (see fb_ibp)                            */
+    uint32_t *s_cand;   /* s_candidates: candidates neither the bound nor the query settled (:349-350)                 */
+    uint32_t *record;   /* [n][2*NW+2] packed per-partition record for the multi-GPU gather: verdict | dead[NW] |
+                         * cand[NW] | first counterexample sample (written as -1; fb_partition_screen_ex fills it)     */
 } fb_prune_out;
 
 /* -- library ---------------------------------------------------------------------------------- */
@@ -89,14 +94,23 @@ int fb_grid_locate(const fb_grid *g, int64_t m, const double *X, int64_t *index,
 int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
                int64_t first_index, uint32_t *counts, void *stream);
 
-/* -- interval bounds + masks: neuron_bounds :105-164, dead_node_from_bound :226-251, keep-one fix,
- *    merge_dead_nodes :941-948.  counts may be NULL (bounds-only run: every neuron is a candidate);
- *    tol [N] may be NULL (no sliver detection). */
+/* -- interval bounds + masks: neuron_bounds :105-164, dead_node_from_bound :226-251, singular_verification*
+ *    :276-644, keep-one fixes, merge_dead_nodes :941-948.  counts may be NULL (bounds-only run: every neuron is a
+ *    candidate).
+ *    Singular verification runs on the device in closed form.  For a remaining candidate j of hidden layer l >= 1 the
+ *    reference's Z3 query boxes input k < out_l by the layer's OWN post-activation bounds pl_lb[l][k], pl_ub[l][k]
+ *    (intermediate_domain_constraint :266-273 is called with layer_index, :302-345) and leaves inputs k >= out_l free, so
+ *    it is unsat -- s_dead = 1 -- iff no free input has a non-zero weight and
+ *        q_j = sum_{k < min(in_l, out_l)} max(w_kj pl_lb[l][k], w_kj pl_ub[l][k]) + b_j <= 0.
+ *    On layer 0 (integer box) the quantity is ws_ub itself.  tol [N] (may be NULL) is the caller's bound on the rounding
+ *    error of that quantity per neuron; neurons with |q_j| <= tol_j are reported in `sliver` so the host can put the
+ *    exact question to Z3.  (For out_l > in_l at l >= 1 the reference raises IndexError; here the sum stops at in_l.) */
 int fb_ibp(const fb_model *m, int64_t n, const int32_t *boxes, const uint32_t *counts, const double *tol,
            const fb_prune_out *out, void *stream);
 
-/* -- the whole pre-solver stage for a batch of boxes: sound_prune*, utils/prune.py:671-859, minus the
- *    Z3 neuron queries (reported through `sliver`).  Allocates [n][N] uint32 of scratch per call. */
+/* -- the whole pre-solver stage for a batch of boxes: sound_prune*, utils/prune.py:671-859; the Z3 neuron
+ *    queries are answered in closed form (fb_ibp), the undecidable ones reported through `sliver`.
+ *    Allocates [n][N] uint32 of scratch per call. */
 int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
              int64_t first_index, const double *tol, const fb_prune_out *out, void *stream);
 

@@ -433,19 +433,63 @@ void fo_forward_f32(int L, const int32_t *dims, const float *W32, const float *B
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * a9: singular_verification*, utils/prune.py:276-644, as the closed form of the query the reference
+ * really poses to Z3.  For a still-candidate neuron j of layer l (layers 0..L-2) it asks whether
+ * {input constraints} and y_j > 0 is satisfiable, y = W_l^T x + b_l, and marks the neuron dead on unsat.
+ *   layer 0 (:297-300): x are Int variables inside the partition box (input_domain_constraint :253-263).
+ *     An affine function attains its supremum over an integer box at a corner, so the query is sat iff
+ *     the exact value of ws_ub[0][j] is > 0.
+ *   layer l >= 1 (:302-340): x are in_l Real variables and the constraints come from
+ *     intermediate_domain_constraint(x, pl_lb, pl_ub, layer_index) (:266-273) -- called with the layer's
+ *     OWN index, so x_k is boxed by pl_lb[l][k] <= x_k <= pl_ub[l][k] for k < out_l (the post-activation
+ *     bounds of layer l itself, index for index) and the inputs k >= out_l stay unbounded.  (For
+ *     out_l > in_l the reference raises IndexError at x[neuron_index]; no reference model has such a
+ *     layer.  Here the constraints stop at min(in_l, out_l).)  The query is therefore sat iff some
+ *     unbounded input has a non-zero weight, or
+ *         q_j = sum_{k < min(in_l, out_l)} max(w_kj * pl_lb[l][k], w_kj * pl_ub[l][k]) + b_j  >  0
+ *     in exact arithmetic.  That is NOT the interval upper bound ws_ub[l][j]: on layers with in_l == out_l
+ *     the reference declares neurons dead whose ws_ub is far above zero (AC-10, src grid partition 13529,
+ *     layer 1 neuron 1: ws_ub = 14.47, q = -10.13, s_dead = 1).  Parity means reproducing exactly that.
+ * q is evaluated like neuron_bounds evaluates its sums: k ascending, product and sum rounded separately,
+ * bias last (Z3 itself is exact, on the decimal repr of every float; the difference is covered by tol).
+ * q[] and unb[] are [N]; entries of layer 0 are (ws_ub, 0), of the last layer (0, 0).
+ * ---------------------------------------------------------------------------------------------- */
+static void singular_one(const fo_net *m, const double *ws_ub, const double *pl_lb, const double *pl_ub,
+                         double *q, uint8_t *unb)
+{
+    for (int l = 0; l < m->L; ++l) {
+        int in = m->dims[l], out = m->dims[l + 1];
+        const double *w = m->W + m->woff[l], *b = m->B + m->boff[l];
+        const double *xl = pl_lb + m->boff[l], *xu = pl_ub + m->boff[l];
+        int mm = in < out ? in : out;
+        for (int j = 0; j < out; ++j) {
+            int64_t o = m->boff[l] + j;
+            unb[o] = 0;
+            if (l == m->L - 1) { q[o] = 0.0; continue; }
+            if (l == 0) { q[o] = ws_ub[o]; continue; }
+            double acc = 0.0;
+            for (int k = 0; k < mm; ++k) {
+                double wt = w[(int64_t)k * out + j];
+                acc += (wt < 0) ? wt * xl[k] : wt * xu[k];
+            }
+            q[o] = acc + b[j];
+            for (int k = out; k < in; ++k) if (w[(int64_t)k * out + j] != 0.0) unb[o] = 1;
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
  * a7 / a8 / a10: dead_node_from_bound (utils/prune.py:226-251), the keep-one fix
  * (:689-691, :698-700, :703-705) and merge_dead_nodes (:941-948), for a batch of partitions.
  *   cand   = count == 0                                   (:183-187, every layer incl. output)
  *   b_dead = cand & (ws_ub <= 0) on layers 0..L-2, = cand on the last layer (:235 break), keep-one
  *   b_cand = cand & !(ws_ub <= 0) on layers 0..L-2, = cand on the last layer
- *   s_dead : the reference asks Z3 whether y_j > 0 is satisfiable on the layer's input box
- *            (:276-356).  The supremum of an affine function over a box is the value neuron_bounds
- *            computes, so Z3 answers sat iff the exact value of ws_ub is > 0.  With a rounding-error
- *            bound tol[j] >= |float ws_ub - exact ws_ub| this is decided without Z3 whenever
- *            ws_ub > tol[j] (sat -> s_dead 0); neurons with 0 < ws_ub <= tol[j] are flagged in
- *            `sliver` for the host to run the reference's own Z3 query.  Last layer: copy of b_cand,
- *            then the keep-one fix clears it (single element list).
- *   dead   = b_dead | s_dead, keep-one (s_dead taken as 0 here; the host ORs in resolved slivers)
+ *   s_dead = b_cand & !unb & (q <= 0) on layers 0..L-2 (singular_one above; on layer 0 q = ws_ub > 0, so 0),
+ *            = b_cand on the last layer (:287-288 break leaves the copy), keep-one
+ *   s_cand = b_cand minus the neurons just found dead (before the keep-one fix, as in :349-350)
+ *   sliver = b_cand & !unb & |q| <= tol[j]: the float sign of q is within rounding error of the exact one;
+ *            the host runs the reference's own Z3 query for these and overrides s_dead / s_cand / dead
+ *   dead   = b_dead | s_dead, keep-one
  * All masks are bytes [n][N].
  * ---------------------------------------------------------------------------------------------- */
 static void keep_one(uint8_t *mask, const fo_net *m)
@@ -457,20 +501,22 @@ static void keep_one(uint8_t *mask, const fo_net *m)
     }
 }
 
-static void masks_one(const fo_net *m, const uint32_t *counts, const double *ws_ub, const double *tol,
-                      uint8_t *cand, uint8_t *b_dead, uint8_t *b_cand, uint8_t *s_dead, uint8_t *dead,
-                      uint8_t *sliver)
+static void masks_one(const fo_net *m, const uint32_t *counts, const double *ws_ub, const double *q,
+                      const uint8_t *unb, const double *tol, uint8_t *cand, uint8_t *b_dead, uint8_t *b_cand,
+                      uint8_t *s_dead, uint8_t *s_cand, uint8_t *dead, uint8_t *sliver)
 {
     for (int l = 0; l < m->L; ++l)
         for (int j = 0; j < m->dims[l + 1]; ++j) {
             int64_t k = m->boff[l] + j;
-            uint8_t c = counts[k] == 0;
+            uint8_t c = counts ? counts[k] == 0 : 1;
             cand[k] = c; sliver[k] = 0;
-            if (l == m->L - 1) { b_dead[k] = c; b_cand[k] = c; s_dead[k] = c; }
+            if (l == m->L - 1) { b_dead[k] = c; b_cand[k] = c; s_dead[k] = c; s_cand[k] = c; }
             else {
                 uint8_t le0 = ws_ub[k] <= 0;
-                b_dead[k] = c & le0; b_cand[k] = c & !le0; s_dead[k] = 0;
-                if (b_cand[k] && ws_ub[k] <= tol[k]) sliver[k] = 1;
+                b_dead[k] = c & le0; b_cand[k] = c & !le0;
+                s_dead[k] = b_cand[k] && !unb[k] && q[k] <= 0;
+                s_cand[k] = b_cand[k] & !s_dead[k];
+                if (tol && b_cand[k] && !unb[k] && fabs(q[k]) <= tol[k]) sliver[k] = 1;
             }
         }
     keep_one(b_dead, m);
@@ -479,16 +525,25 @@ static void masks_one(const fo_net *m, const uint32_t *counts, const double *ws_
     keep_one(dead, m);
 }
 
-void fo_masks(int L, const int32_t *dims, int64_t n, const uint32_t *counts, const double *ws_ub,
-              const double *tol, uint8_t *cand, uint8_t *b_dead, uint8_t *b_cand, uint8_t *s_dead,
-              uint8_t *dead, uint8_t *sliver)
+void fo_masks(int L, const int32_t *dims, const double *W, const double *B, int64_t n, const uint32_t *counts,
+              const double *ws_ub, const double *pl_lb, const double *pl_ub, const double *tol, uint8_t *cand,
+              uint8_t *b_dead, uint8_t *b_cand, uint8_t *s_dead, uint8_t *s_cand, uint8_t *dead, uint8_t *sliver,
+              double *q_out)
 {
-    fo_net m; if (fo_net_init(&m, L, dims, NULL, NULL)) return;
-#pragma omp parallel for schedule(static)
-    for (int64_t p = 0; p < n; ++p) {
-        int64_t o = p * m.N;
-        masks_one(&m, counts + o, ws_ub + o, tol, cand + o, b_dead + o, b_cand + o, s_dead + o, dead + o,
-                  sliver + o);
+    fo_net m; if (fo_net_init(&m, L, dims, W, B)) return;
+#pragma omp parallel
+    {
+        double *q = (double *)malloc(sizeof(double) * m.N);
+        uint8_t *unb = (uint8_t *)malloc(m.N);
+#pragma omp for schedule(static)
+        for (int64_t p = 0; p < n; ++p) {
+            int64_t o = p * m.N;
+            singular_one(&m, ws_ub + o, pl_lb + o, pl_ub + o, q, unb);
+            masks_one(&m, counts ? counts + o : NULL, ws_ub + o, q, unb, tol, cand + o, b_dead + o, b_cand + o,
+                      s_dead + o, s_cand + o, dead + o, sliver + o);
+            if (q_out) memcpy(q_out + o, q, sizeof(double) * m.N);
+        }
+        free(q); free(unb);
     }
 }
 
@@ -664,17 +719,18 @@ void fo_partition_screen(int L, const int32_t *dims, const float *W32, const flo
  * ---------------------------------------------------------------------------------------------- */
 void fo_prune_batch(int L, const int32_t *dims, const double *W, const double *B, int64_t n,
                     const int32_t *boxes, uint64_t seed, int64_t first_index, int S, const double *tol,
-                    uint32_t *counts, uint8_t *cand, uint8_t *b_dead, uint8_t *dead, uint8_t *sliver,
-                    uint8_t *verdict)
+                    uint32_t *counts, uint8_t *cand, uint8_t *b_dead, uint8_t *s_dead, uint8_t *dead,
+                    uint8_t *sliver, uint8_t *verdict)
 {
     fo_net m; if (fo_net_init(&m, L, dims, W, B)) return;
     int d = dims[0];
 #pragma omp parallel
     {
-        double *buf = (double *)malloc(sizeof(double) * (m.maxw * 4 + 6 * m.N));
+        double *buf = (double *)malloc(sizeof(double) * (m.maxw * 4 + 7 * m.N));
         double *wl = buf + m.maxw * 4, *wu = wl + m.N, *pl = wu + m.N, *pu = pl + m.N, *rd = pu + m.N, *ru = rd + m.N;
+        double *q = ru + m.N;
         int32_t *xi = (int32_t *)malloc(sizeof(int32_t) * d);
-        uint8_t *bc = (uint8_t *)malloc(2 * m.N), *sd = bc + m.N;
+        uint8_t *bc = (uint8_t *)malloc(3 * m.N), *sc = bc + m.N, *unb = sc + m.N;
 #pragma omp for schedule(static)
         for (int64_t p = 0; p < n; ++p) {
             const int32_t *box = boxes + p * d * 2;
@@ -687,8 +743,9 @@ void fo_prune_batch(int L, const int32_t *dims, const double *W, const double *B
             }
             ibp_one(&m, box, buf, wl, wu, pl, pu);
             ibp_directed_one(&m, box, buf, rd, ru);
-            masks_one(&m, c, wu, tol, cand + p * m.N, b_dead + p * m.N, bc, sd, dead + p * m.N,
-                      sliver + p * m.N);
+            singular_one(&m, wu, pl, pu, q, unb);
+            masks_one(&m, c, wu, q, unb, tol, cand + p * m.N, b_dead + p * m.N, bc, s_dead + p * m.N, sc,
+                      dead + p * m.N, sliver + p * m.N);
             uint8_t v = 0;
             if (rd[m.N - 1] > 0 || ru[m.N - 1] < 0) v |= 1;
             for (int k = 0; k < m.N; ++k) if (sliver[p * m.N + k]) v |= 4;

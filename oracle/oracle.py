@@ -126,12 +126,23 @@ def forward_f32(net, X):
     return out
 
 
-def masks(net, counts, ws_ub, tol):
-    counts = np.ascontiguousarray(counts, dtype=np.uint32); n = counts.shape[0]
-    ws_ub = np.ascontiguousarray(ws_ub, dtype=np.float64); tol = np.ascontiguousarray(tol, dtype=np.float64)
-    names = ("cand", "b_dead", "b_cand", "s_dead", "dead", "sliver")
+def masks(net, counts, ws_ub, pl_lb, pl_ub, tol=None):
+    """Mask algebra of sound_prune* for [n, N] inputs (counts may be None: every neuron a candidate).  Returns byte
+    masks cand, b_dead, b_cand, s_dead, s_cand, dead, sliver and `q`, the float value of the quantity the
+    reference's Z3 neuron query decides the sign of (see singular_one in fairify_oracle.c)."""
+    ws_ub = np.ascontiguousarray(ws_ub, dtype=np.float64); n = ws_ub.shape[0]
+    if counts is not None:
+        counts = np.ascontiguousarray(counts, dtype=np.uint32)
+    pl_lb = np.ascontiguousarray(pl_lb, dtype=np.float64); pl_ub = np.ascontiguousarray(pl_ub, dtype=np.float64)
+    if tol is not None:
+        tol = np.ascontiguousarray(tol, dtype=np.float64)
+    names = ("cand", "b_dead", "b_cand", "s_dead", "s_cand", "dead", "sliver")
     outs = {k: np.zeros((n, net.N), dtype=np.uint8) for k in names}
-    lib().fo_masks(net.L, _p(net.dims), C.c_int64(n), _p(counts), _p(ws_ub), _p(tol), *[_p(outs[k]) for k in names])
+    q = np.zeros((n, net.N))
+    lib().fo_masks(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), _p(counts) if counts is not None else None,
+                   _p(ws_ub), _p(pl_lb), _p(pl_ub), _p(tol) if tol is not None else None,
+                   *[_p(outs[k]) for k in names], _p(q))
+    outs["q"] = q
     return outs
 
 
@@ -172,7 +183,7 @@ def prune_batch(net, boxes, seed, first_index, S, tol):
     boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
     tol = np.ascontiguousarray(tol, dtype=np.float64)
     counts = np.zeros((n, net.N), dtype=np.uint32)
-    names = ("cand", "b_dead", "dead", "sliver")
+    names = ("cand", "b_dead", "s_dead", "dead", "sliver")
     outs = {k: np.zeros((n, net.N), dtype=np.uint8) for k in names}
     verdict = np.zeros(n, dtype=np.uint8)
     lib().fo_prune_batch(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), _p(boxes), C.c_uint64(seed),
@@ -191,12 +202,15 @@ def set_threads(n):
 
 
 def sliver_tolerance(net, lo, hi):
-    """Per-neuron bound on |float ws_ub - exact ws_ub| valid for every box inside [lo, hi].
+    """Per-neuron tolerance below which the float sign of the singular-verification quantity is not trusted, valid
+    for every box inside [lo, hi].
 
-    Standard recursive-summation bound: (in+1) roundings of relative size 2^-53 on terms whose
-    magnitudes sum to at most M_j = sum_i |w_ij| * max|x_i| + |b_j|, with a x4 safety factor.  The same
-    formula is used by the host library (fairify_b200.engine.sliver_tolerance); kept separately here so
-    the oracle stays self-contained.
+    Layer 0: the quantity is ws_ub; (in+2) roundings of relative size 2^-53 on terms whose magnitudes sum to at most
+    M_j = sum_i |w_ij| * max|x_i| + |b_j|.  Layer l >= 1: the quantity is q_j (singular_one in fairify_oracle.c), a sum
+    over the first min(in, out) inputs bounded by the layer's OWN post-activation magnitudes M_l, so the terms sum to at
+    most sum_k |w_kj| M_l[k] + |b_j|; Z3 additionally reads every float through its decimal repr (one more relative
+    2^-53 per factor).  Both with a x4 safety factor.  The same formula is used by the host library
+    (fairify_b200.engine.sliver_tolerance); kept separately here so the oracle stays self-contained.
     """
     mag = np.maximum(np.abs(np.asarray(lo, dtype=np.float64)), np.abs(np.asarray(hi, dtype=np.float64)))
     tol = np.zeros(net.N)
@@ -206,6 +220,11 @@ def sliver_tolerance(net, lo, hi):
         w = np.abs(net.W[wo:wo + i * o].reshape(i, o)); wo += i * o
         b = np.abs(net.B[net.boff[l]:net.boff[l + 1]])
         M = mag @ w + b
-        tol[net.boff[l]:net.boff[l + 1]] = 4.0 * (i + 2) * 2.0 ** -53 * M
+        if l == 0:
+            t = 4.0 * (i + 2) * 2.0 ** -53 * M
+        else:
+            mm = min(i, o)
+            t = 4.0 * (mm + 4) * 2.0 ** -53 * (M[:mm] @ w[:mm] + b)
+        tol[net.boff[l]:net.boff[l + 1]] = t
         mag = M
     return tol

@@ -36,6 +36,8 @@ class Golden:
         self.stats = np.load(os.path.join(GOLD, "np_stats.npz"))
         self.causal = np.load(os.path.join(GOLD, "causal_cases.npz"))
         self.models = [str(m) for m in self.prune["models"]]
+        self.singular = np.load(os.path.join(GOLD, "singular_cases.npz"))
+        self.singular_models = [str(m) for m in self.singular["models"]]
 
     def model_names(self):
         return sorted({k.split("/")[0] for k in self.weights.files})
@@ -52,6 +54,17 @@ class Golden:
             c["samples"] = reference_samples(c["seed"], c["box"], c["S"])
             sha = hashlib.sha256(c["samples"].tobytes()).digest()
             assert sha == c["sim_sha256"].tobytes(), "regenerated samples differ from the reference's"
+            c["tag"] = tag
+            yield c
+
+    def singular_cases(self, name):
+        """One model's full-Z3 sound_prune* cases (make_golden.py singular): seed = canonical partition index."""
+        z = self.singular
+        for k in range(int(z[f"{name}/ncases"])):
+            tag = f"{name}/{k}"
+            c = {f.split("/")[-1]: z[f] for f in z.files if f.startswith(tag + "/")}
+            c["samples"] = reference_samples(c["index"], c["box"], c["S"])
+            assert hashlib.sha256(c["samples"].tobytes()).digest() == c["sim_sha256"].tobytes()
             c["tag"] = tag
             yield c
 

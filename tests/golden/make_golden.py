@@ -24,6 +24,7 @@ import glob
 import hashlib
 import os
 import sys
+import types
 
 import numpy as np
 import pandas as pd
@@ -300,5 +301,104 @@ def density_case(ref):
     np.savez_compressed(os.path.join(HERE, "density.npz"), **out)
 
 
+# ----------------------------------------------------------------------------------------------------
+# full sound_prune* INCLUDING the Z3 singular_verification (utils/prune.py:276-644) on every model with a
+# hidden layer whose input and output widths are equal.  There the reference's query bounds the inputs of layer
+# l >= 1 with that layer's OWN post-activation bounds (intermediate_domain_constraint is called with
+# layer_index, :266-273, :302-345), so it answers unsat -- s_dead = 1 -- for neurons whose interval upper bound is
+# far above 0.  Z3 is slow (0.05-0.5 s per neuron), so the cases are spread over worker processes.
+#     python tests/golden/make_golden.py singular        # writes tests/golden/singular_cases.npz
+# ----------------------------------------------------------------------------------------------------
+# (CP-2..CP-10 take 12 features, but singular_verification_compass hard-codes 6 -- z3_layer1_ws_net_compass,
+#  utils/prune.py:74-79 -- and raises IndexError on them; the 32-32 COMPAS shape is covered by CP-11, d = 6.)
+SINGULAR_MODELS = ["AC-4", "AC-5", "AC-6", "AC-8", "AC-9", "AC-10", "AC-11", "AC-12", "BM-6", "BM-7", "CP-11",
+                   "AC-1", "GC-4", "BM-8"]          # the last three: funnel layers (inputs k >= out stay unbounded)
+SINGULAR_PER_MODEL = 20
+SINGULAR_FORCED = {"AC-10": [13529, 5595]}            # partitions on which the verdict of round 1 saw s_dead = 1
+_sing_state = {}
+
+
+def _singular_domain(name):
+    return domains.DOMAINS[name.split("-")[0]]
+
+
+def _singular_worker(task):
+    name, idx, S = task
+    if "ref" not in _sing_state:
+        _sing_state["ref"] = refshim.load()
+        _sing_state["weights"] = np.load(os.path.join(HERE, "weights.npz"))
+    ref, weights = _sing_state["ref"], _sing_state["weights"]
+    P = ref.prune
+    dom = name.split("-")[0]
+    sound = {"AC": P.sound_prune, "GC": P.sound_prune_german, "BM": P.sound_prune_bank, "CP": P.sound_prune_compass}[dom]
+    D = _singular_domain(name)
+    L = int(weights[f"{name}/L"])
+    w64 = [weights[f"{name}/w{l}"].astype(np.float64) for l in range(L)]
+    b64 = [weights[f"{name}/b{l}"].astype(np.float64) for l in range(L)]
+    layer_net, _ = refshim.model_functions(name)
+    df = pd.DataFrame(np.zeros((2, D.d + 1)), columns=D.columns + [D.label])
+    rd = D.copy_ranges()
+    key = (name, "plist")
+    if key not in _sing_state:
+        p_dict = ref.input_partition.partition(rd, D.threshold)
+        _sing_state[key] = ref.input_partition.partitioned_ranges(rd.keys(), D.pa, p_dict, rd)
+    p = _sing_state[key][idx]
+    np.random.seed(idx)
+    with refshim.quiet():
+        bounds, cand, s_cand, b_dead, s_dead, dead, pos_prob, sim_df = sound(df, w64, b64, S, layer_net, p)
+    ws_lb, ws_ub, pl_lb, pl_ub = bounds
+    sim = sim_df.to_numpy()
+    return {"model": name, "index": idx, "S": S, "box": box_array(p, D.columns),
+            "sim_sha256": np.frombuffer(hashlib.sha256(sim.astype(np.int32).tobytes()).digest(), dtype=np.uint8),
+            "cand": flat_u8(cand), "s_cand": flat_u8(s_cand), "b_dead": flat_u8(b_dead), "s_dead": flat_u8(s_dead),
+            "dead": flat_u8(dead), "ws_ub": flat(ws_ub), "pl_lb": flat(pl_lb), "pl_ub": flat(pl_ub),
+            "pos_prob": flat(pos_prob), "s_compression": np.float64(P.compression_ratio(s_dead)),
+            "st_compression": np.float64(P.compression_ratio(dead))}
+
+
+def singular_cases():
+    import multiprocessing as mp
+    weights = np.load(os.path.join(HERE, "weights.npz"))
+    tasks = []
+    for name in SINGULAR_MODELS:
+        D = _singular_domain(name)
+        rd = D.copy_ranges()
+        n = 1
+        for lo, hi in rd.values():
+            size = hi - lo + 1
+            n *= 1 if size <= D.threshold else -(-size // D.threshold)
+        rng = np.random.RandomState(sum(map(ord, name)))
+        count = 40 if name == "AC-5" else SINGULAR_PER_MODEL
+        idxs = list(SINGULAR_FORCED.get(name, []))
+        while len(idxs) < min(count, n):
+            k = int(rng.randint(0, n))
+            if k not in idxs:
+                idxs.append(k)
+        tasks += [(name, k, 200) for k in idxs]
+    # biggest models first so the pool drains evenly
+    order = {m: i for i, m in enumerate(["AC-4", "BM-7", "AC-5", "CP-11", "AC-11", "AC-12"])}
+    tasks.sort(key=lambda t: order.get(t[0], 99))
+    with mp.get_context("fork").Pool(min(8, os.cpu_count() or 1)) as pool:
+        results = pool.map(_singular_worker, tasks, chunksize=1)
+    out = {}
+    per_model = {}
+    for r in results:
+        k = per_model.setdefault(r["model"], 0)
+        per_model[r["model"]] = k + 1
+        tag = f"{r['model']}/{k}"
+        for key, v in r.items():
+            if key != "model":
+                out[f"{tag}/{key}"] = np.asarray(v)
+    for m, k in per_model.items():
+        out[f"{m}/ncases"] = np.int64(k)
+        hits = sum(int(out[f"{m}/{i}/s_dead"].sum()) for i in range(k))
+        print(f"singular cases {m}: {k} partitions, {hits} neurons with s_dead = 1")
+    out["models"] = np.array(list(per_model.keys()))
+    np.savez_compressed(os.path.join(HERE, "singular_cases.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "singular":
+        singular_cases()
+    else:
+        main()

@@ -60,8 +60,8 @@ def test_profile_and_masks(name):
         S = int(c["S"])
         assert np.array_equal(counts[0] == 0, c["cand"].astype(bool)), c["tag"]
         assert np.array_equal(counts[0] / S, c["pos_prob"]), c["tag"]
-        ws_ub = O.ibp(net, c["box"][None])[1]
-        m = O.masks(net, counts, ws_ub, tol)
+        _, ws_ub, pl_lb, pl_ub = O.ibp(net, c["box"][None])
+        m = O.masks(net, counts, ws_ub, pl_lb, pl_ub, tol)
         assert np.array_equal(m["cand"][0], c["cand"])
         assert np.array_equal(m["b_dead"][0], c["b_dead"]), c["tag"]
         assert np.array_equal(m["b_cand"][0], c["b_cand"]), c["tag"]
@@ -70,9 +70,49 @@ def test_profile_and_masks(name):
         if "dead" in c:       # full sound_prune* run including the Z3 singular_verification
             assert np.array_equal(m["s_dead"][0], c["s_dead"]), c["tag"]
             assert np.array_equal(m["dead"][0], c["dead"]), c["tag"]
-            assert np.array_equal(m["b_cand"][0], c["s_cand"]), c["tag"]
+            assert np.array_equal(m["s_cand"][0], c["s_cand"]), c["tag"]
             assert O.compression_ratio(m["dead"][0]) == float(c["st_compression"])
-            assert float(c["s_compression"]) == 0.0
+            assert O.compression_ratio(m["s_dead"][0]) == float(c["s_compression"])
+
+
+@pytest.mark.parametrize("name", G.singular_models)
+def test_singular_verification_closed_form(name):
+    """sound_prune* INCLUDING the Z3 singular_verification (utils/prune.py:276-644) on every model with a hidden layer
+    of equal input and output width (plus three funnels): the reference bounds a layer's inputs with that layer's own
+    post-activation bounds (:266-273 called with layer_index, :302-345), so it finds neurons dead whose interval upper
+    bound is far above zero.  The closed form must give the reference's s_dead / s_candidates / dead_nodes exactly."""
+    net = O.Net(*G.wb(name))
+    dom = G.domain(name)
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    tol = O.sliver_tolerance(net, lo, hi)
+    hits = 0
+    for c in G.singular_cases(name):
+        counts = O.profile(net, c["samples"][None])
+        _, ws_ub, pl_lb, pl_ub = O.ibp(net, c["box"][None])
+        assert np.array_equal(ws_ub[0], c["ws_ub"]) and np.array_equal(pl_lb[0], c["pl_lb"]) and np.array_equal(pl_ub[0], c["pl_ub"])
+        m = O.masks(net, counts, ws_ub, pl_lb, pl_ub, tol)
+        for k in ("cand", "b_dead", "s_dead", "s_cand", "dead"):
+            assert np.array_equal(m[k][0], c[k]), f"{c['tag']} {k}"
+        assert not m["sliver"].any(), c["tag"]
+        assert O.compression_ratio(m["dead"][0]) == float(c["st_compression"])
+        assert O.compression_ratio(m["s_dead"][0]) == float(c["s_compression"])
+        hits += int(c["s_dead"].sum())
+        if hits:          # a neuron Z3 found dead although its interval bound is positive
+            sd = c["s_dead"].astype(bool)
+            assert np.all(c["ws_ub"][sd] > 0)
+    if name in ("AC-4", "AC-8", "AC-10", "AC-12", "BM-6", "BM-7"):
+        assert hits > 0, "the fixtures of this model hold partitions where the reference's Z3 pass finds a neuron"
+
+
+def test_singular_verification_ac10_partition_13529():
+    """The partition the round-1 review named: src/AC grid index 13529, layer 1 neuron 1, ws_ub = 14.47, s_dead = 1."""
+    net = O.Net(*G.wb("AC-10"))
+    c = next(c for c in G.singular_cases("AC-10") if int(c["index"]) == 13529)
+    j = int(net.boff[1]) + 1
+    assert c["s_dead"][j] == 1 and abs(c["ws_ub"][j] - 14.466598695433476) < 1e-9
+    _, ws_ub, pl_lb, pl_ub = O.ibp(net, c["box"][None])
+    m = O.masks(net, O.profile(net, c["samples"][None]), ws_ub, pl_lb, pl_ub, None)
+    assert m["s_dead"][0][j] == 1 and m["q"][0][j] < -10.0 and m["dead"][0][j] == 1
 
 
 def test_known_answers_from_the_reference_notebook():
