@@ -13,7 +13,8 @@ SO_PATH = os.environ.get("FAIRIFY_B200_LIB") or os.path.join(_HERE, "libfairify_
 
 # every symbol include/fairify_b200.h declares
 EXPORTS = [
-    "fb_version", "fb_last_error", "fb_num_sms", "fb_model_create", "fb_model_destroy", "fb_model_info",
+    "fb_version", "fb_last_error", "fb_num_sms", "fb_model_create", "fb_model_destroy", "fb_model_info", "fb_model_device",
+    "fb_release_cache",
     "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_grid_locate", "fb_profile", "fb_ibp", "fb_prune",
     "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_heuristic", "fb_fp64_peak",
 ]
@@ -49,6 +50,8 @@ def lib():
     L.fb_model_create.argtypes = [i32, vp, vp, vp, C.POINTER(vp)]
     L.fb_model_destroy.argtypes = [vp]; L.fb_model_destroy.restype = None
     L.fb_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.fb_model_device.argtypes = [vp, C.POINTER(i32)]
+    L.fb_release_cache.argtypes = []
     L.fb_grid_create.argtypes = [i32, vp, vp, i64, vp, C.POINTER(vp)]
     L.fb_grid_destroy.argtypes = [vp]; L.fb_grid_destroy.restype = None
     L.fb_grid_size.argtypes = [vp]; L.fb_grid_size.restype = i64

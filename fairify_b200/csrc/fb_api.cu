@@ -13,7 +13,12 @@
 #include "../../include/fairify_b200.h"
 #include "fb_generic.cuh"
 #include "fb_launch.cuh"
+#include "fb_mma.cuh"
 #include "fb_registry.h"
+
+cudaError_t fb_profile_mma(const FbMmaNet &net, int64_t n, const int32_t *boxes, const int32_t *samples, uint64_t seed,
+                           int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *counts, int num_sms,
+                           cudaStream_t st);      // fb_mma.cu
 
 static_assert(sizeof(fb_prune_out) == sizeof(FbPruneOut), "fb_prune_out and FbPruneOut must match");
 
@@ -65,10 +70,13 @@ struct fb_model {
     const FbSpecFwdEntry *spec = nullptr;               // compile-time-specialised kernels for this shape, if any
     const FbSpecProfileEntry *spec_profile = nullptr;
     const FbSpecIbpEntry *spec_ibp = nullptr;           // (its launcher is null for shapes left to the runtime-shape kernel)
+    const FbSpecMmaEntry *spec_mma = nullptr;           // shape-specialised DMMA profile kernel (the wide networks)
     void *p64 = nullptr, *p32 = nullptr;
     FbTileNet tile{};               // padded float64 weights for the tiled profile kernel
     double *dWpad = nullptr;
     float *dWpad32 = nullptr;
+    FbMmaNet mma{};                 // fragment-major weights for the DMMA profile kernel
+    double *dWf = nullptr, *dBp = nullptr;
     uint32_t *dUnb = nullptr;       // per neuron: a non-zero weight on an input the singular-verification query leaves unbounded
 };
 
@@ -121,12 +129,13 @@ static const E *fb_find_spec(const FbSpecTableT<E> *const (&tables)[NT], int L, 
 static const FbSpecFwdTable *const fb_fwd_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_F)};
 static const FbSpecProfileTable *const fb_profile_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_P)};
 static const FbSpecIbpTable *const fb_ibp_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_I)};
+static const FbSpecMmaTable *const fb_mma_tables[] = {&fb_spec_mma_table_a, &fb_spec_mma_table_b, &fb_spec_mma_table_c};
 
 extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32); cudaFree(m->dUnb);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32); cudaFree(m->dUnb); cudaFree(m->dWf); cudaFree(m->dBp);
     delete m;
 }
 
@@ -215,9 +224,51 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
         t.Wp = m->dWpad; t.B = m->dB64; t.Wp32 = m->dWpad32; t.B32 = m->dB32;
     }
+    {
+        // weights in the operand order of the FP64 matrix instruction, columns of every tile permuted (fb_mma.cuh)
+        FbMmaNet &q = m->mma;
+        q.L = L; q.N = g.N;
+        int wo = 0, bo2 = 0;
+        for (int l = 0; l <= L; ++l) { q.dims[l] = g.dims[l]; q.boff[l] = g.boff[l]; }
+        q.maxnb = ((g.dims[0] + 3) / 4 + 1) / 2;
+        for (int l = 0; l < L; ++l) {
+            q.kb[l] = (g.dims[l] + 3) / 4; q.nb[l] = (g.dims[l + 1] + 7) / 8;
+            q.maxnb = std::max(q.maxnb, q.nb[l]);
+            q.woff[l] = wo; q.bpoff[l] = bo2;
+            wo += q.kb[l] * q.nb[l] * 32;
+            bo2 += q.nb[l] * 8;
+        }
+        q.woff[L] = wo; q.bpoff[L] = bo2; q.wtotal = wo; q.btotal = bo2;
+        std::vector<double> wf((size_t)wo, 0.0), bp((size_t)bo2, 0.0);
+        for (int l = 0; l < L; ++l) {
+            const int IN = g.dims[l], OUT = g.dims[l + 1];
+            const double *W = m->hW64.data() + g.woff[l];
+            const int KB = q.kb[l], NB = q.nb[l];
+            for (int tile = 0; tile < NB; ++tile) {
+                const int cg = tile / FB_MMA_NT, nt = tile % FB_MMA_NT, ntg = std::min(FB_MMA_NT, NB - cg * FB_MMA_NT);
+                for (int c = 0; c < 8; ++c) {
+                    const int j = 8 * tile + fb_mma_col_neuron(c);
+                    if (j < OUT) bp[(size_t)q.bpoff[l] + 8 * tile + c] = m->hB64[(size_t)g.boff[l] + j];
+                }
+                for (int kb = 0; kb < KB; ++kb)
+                    for (int lane = 0; lane < 32; ++lane) {
+                        const int k = 4 * kb + (lane & 3), j = 8 * tile + fb_mma_col_neuron(lane >> 2);
+                        if (k < IN && j < OUT)
+                            wf[(size_t)q.woff[l] + ((size_t)cg * KB * FB_MMA_NT + (size_t)kb * ntg + nt) * 32 + lane] = W[(size_t)k * OUT + j];
+                    }
+            }
+        }
+        e = cudaMalloc(&m->dWf, sizeof(double) * wf.size());
+        if (e == cudaSuccess) e = cudaMalloc(&m->dBp, sizeof(double) * bp.size());
+        if (e == cudaSuccess) e = cudaMemcpy(m->dWf, wf.data(), sizeof(double) * wf.size(), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(m->dBp, bp.data(), sizeof(double) * bp.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
+        q.Wf = m->dWf; q.Bp = m->dBp;
+    }
     m->spec = fb_find_spec(fb_fwd_tables, L, dims);
     m->spec_profile = fb_find_spec(fb_profile_tables, L, dims);
     m->spec_ibp = fb_find_spec(fb_ibp_tables, L, dims);
+    m->spec_mma = fb_find_spec(fb_mma_tables, L, dims);
     if (!m->spec_profile || !m->spec_ibp) m->spec = nullptr;
     if (m->spec && !fb_model_subnormal_free(g, m->hW64, m->hB64)) m->spec = nullptr;   // runtime-shape kernels: exact sign test
     if (m->spec) {
@@ -239,19 +290,48 @@ extern "C" int fb_model_info(const fb_model *m, int *L, int *N, int *P, int *spe
     return FB_OK;
 }
 
-// Scratch and staging buffers come from the device's stream-ordered pool.  By default that pool hands memory back
-// to the driver at every synchronisation, so a caller looping over fb_prune_host would re-acquire gigabytes per
-// call; keep freed blocks cached in the pool instead (once per device).
-static void fb_pool_keep_cached(int device)
+// Scratch and staging buffers come from a stream-ordered memory pool that belongs to this library (one per device,
+// created on first use), not from the device's default pool: freed blocks stay cached in it between calls -- a caller
+// looping over fb_prune_host would otherwise re-acquire gigabytes from the driver per call -- without changing the
+// release behaviour of a pool the embedding application may share.  fb_release_cache() hands the cached memory back.
+static std::mutex fb_pool_mu;
+static cudaMemPool_t fb_pools[64] = {};
+
+static cudaError_t fb_pool_for(int device, cudaMemPool_t *out)
 {
-    static bool done[64] = {};
-    if (device < 0 || device >= 64 || done[device]) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(fb_pool_mu);
+    if (!fb_pools[device]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaMemPool_t pool;
+        cudaError_t e = cudaMemPoolCreate(&pool, &props);
+        if (e != cudaSuccess) return e;
         unsigned long long keep = ~0ull;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        fb_pools[device] = pool;
     }
-    done[device] = true;
+    *out = fb_pools[device];
+    return cudaSuccess;
+}
+
+static cudaError_t fb_malloc_async(void **p, size_t bytes, int device, cudaStream_t st)
+{
+    cudaMemPool_t pool;
+    cudaError_t e = fb_pool_for(device, &pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(p, bytes ? bytes : 1, pool, st);
+}
+
+extern "C" int fb_release_cache(void)
+{
+    std::lock_guard<std::mutex> lock(fb_pool_mu);
+    for (int d = 0; d < 64; ++d)
+        if (fb_pools[d]) FB_CUDA(cudaMemPoolTrimTo(fb_pools[d], 0));
+    return FB_OK;
 }
 
 // set FAIRIFY_B200_FORCE_GENERIC=1 to route every model through the runtime-shape kernels (tests)
@@ -397,9 +477,27 @@ static void fb_pick_chunks(const fb_model *m, int64_t n, int S, int *chunks, int
     *chunks = std::max(c, 1); *chunk_len = len;
 }
 
+// every launch uses the model's device buffers: the model's device must be the current one
+static int fb_check_device(const char *fn, const fb_model *m)
+{
+    int dev = -1;
+    FB_CUDA(cudaGetDevice(&dev));
+    if (dev != m->device)
+        return fb_fail(FB_ERR_INVALID, "%s: the model lives on device %d but device %d is current", fn, m->device, dev);
+    return FB_OK;
+}
+
+extern "C" int fb_model_device(const fb_model *m, int *device)
+{
+    if (!m || !device) return fb_fail(FB_ERR_INVALID, "fb_model_device: null argument");
+    *device = m->device;
+    return FB_OK;
+}
+
 static int fb_check_batch(const char *fn, const fb_model *m, int64_t n, const void *boxes, int S, bool need_s)
 {
     if (!m) return fb_fail(FB_ERR_INVALID, "%s: null model", fn);
+    if (int rc = fb_check_device(fn, m)) return rc;
     if (n < 0) return fb_fail(FB_ERR_INVALID, "%s: n = %lld", fn, (long long)n);
     if (n > 0 && !boxes) return fb_fail(FB_ERR_INVALID, "%s: null boxes", fn);
     if (need_s && (S < 1 || S > 65535)) return fb_fail(FB_ERR_INVALID, "%s: S = %d (supported: 1..65535)", fn, S);
@@ -416,6 +514,15 @@ static bool fb_use_tiled_profile(const fb_model *m)
     static const int forced = [] { const char *v = getenv("FAIRIFY_B200_TILED_PROFILE"); return !v ? -1 : (v[0] == '0' ? 0 : 1); }();
     if (forced >= 0) return forced == 1;
     return m->gen.P >= 4000;
+}
+
+// FAIRIFY_B200_MMA_PROFILE=1 sends every runtime-shape profile through the DMMA kernel, =0 none (tests, comparisons);
+// by default the networks that used to take the tiled kernel do.
+static bool fb_use_mma_profile(const fb_model *m)
+{
+    static const int forced = [] { const char *v = getenv("FAIRIFY_B200_MMA_PROFILE"); return !v ? -1 : (v[0] == '0' ? 0 : 1); }();
+    if (forced >= 0) return forced == 1;
+    return fb_use_tiled_profile(m);
 }
 
 template <int TM, bool RESIDENT>
@@ -509,6 +616,14 @@ extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, co
                                  counts, m->num_sms, st));
         return FB_OK;
     }
+    if (fb_use_mma_profile(m)) {
+        static const bool generic_mma = [] { const char *v = getenv("FAIRIFY_B200_MMA_GENERIC"); return v && v[0] == '1'; }();
+        if (m->spec_mma && !generic_mma)
+            FB_CUDA(m->spec_mma->profile(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
+        else
+            FB_CUDA(fb_profile_mma(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
+        return FB_OK;
+    }
     if (fb_use_tiled_profile(m)) return fb_profile_tiled(m, n, boxes, samples, S, seed, first_index, counts, chunks > 1, st);
     const size_t smem = fb_profile_gen_smem(m);
     if (smem > 227 * 1024) return fb_fail(FB_ERR_UNSUPPORTED, "fb_profile: model needs %zu bytes of shared memory", smem);
@@ -560,8 +675,7 @@ extern "C" int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, cons
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     uint32_t *counts = nullptr;
-    fb_pool_keep_cached(m->device);
-    FB_CUDA(cudaMallocAsync(&counts, sizeof(uint32_t) * n * m->gen.N, st));
+    FB_CUDA(fb_malloc_async((void **)&counts, sizeof(uint32_t) * n * m->gen.N, m->device, st));
     int rc = fb_profile(m, n, boxes, samples, S, seed, first_index, counts, stream);
     if (rc == FB_OK) rc = fb_ibp(m, n, boxes, counts, tol, out, stream);
     cudaFreeAsync(counts, st);
@@ -572,10 +686,11 @@ extern "C" int fb_prune(const fb_model *m, int64_t n, const int32_t *boxes, cons
 namespace {
 struct DevBuf {
     void *p = nullptr;
+    int device;
     cudaStream_t st;
-    explicit DevBuf(cudaStream_t s) : st(s) {}
+    DevBuf(int dev, cudaStream_t s) : device(dev), st(s) {}
     ~DevBuf() { if (p) cudaFreeAsync(p, st); }
-    cudaError_t alloc(size_t bytes) { return cudaMallocAsync(&p, bytes ? bytes : 1, st); }
+    cudaError_t alloc(size_t bytes) { return fb_malloc_async(&p, bytes, device, st); }
 };
 }  // namespace
 
@@ -606,12 +721,11 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
     if (n == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const int N = m->gen.N, NW = (N + 31) / 32, d = m->gen.dims[0];
-    fb_pool_keep_cached(m->device);
     cudaStream_t up, down;
     if (int rc = fb_copy_streams(m->device, &up, &down)) return rc;
 
     // device copies of the inputs and one device buffer per requested output (whole batch; freed on `st` at return)
-    DevBuf dboxes(st), dsamp(st), dtol(st);
+    DevBuf dboxes(m->device, st), dsamp(m->device, st), dtol(m->device, st);
     FB_CUDA(dboxes.alloc(sizeof(int32_t) * n * d * 2));
     if (samples) FB_CUDA(dsamp.alloc(sizeof(int32_t) * n * S * d));
     if (tol) {
@@ -635,7 +749,7 @@ extern "C" int fb_prune_host(const fb_model *m, int64_t n, const int32_t *boxes,
     bufs.reserve(sizeof(slots) / sizeof(slots[0]));
     for (Slot &s : slots) {
         if (!s.host) continue;
-        bufs.emplace_back(st);
+        bufs.emplace_back(m->device, st);
         FB_CUDA(bufs.back().alloc(s.row_bytes * n));
         s.dev = bufs.back().p;
     }
@@ -707,6 +821,7 @@ extern "C" int fb_forward_f64(const fb_model *m, int64_t rows, const double *X, 
                               void *stream)
 {
     if (!m || rows < 0 || (rows > 0 && (!X || !logits))) return fb_fail(FB_ERR_INVALID, "fb_forward_f64: bad argument");
+    if (int rc = fb_check_device("fb_forward_f64", m)) return rc;
     if (rows == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (fb_use_spec(m)) { FB_CUDA(m->spec->forward64(m->p64, rows, X, dead_bits, logits, m->num_sms, st)); return FB_OK; }
@@ -721,6 +836,7 @@ extern "C" int fb_forward_f32(const fb_model *m, int64_t rows, const float *X, c
                               void *stream)
 {
     if (!m || rows < 0 || (rows > 0 && (!X || !logits))) return fb_fail(FB_ERR_INVALID, "fb_forward_f32: bad argument");
+    if (int rc = fb_check_device("fb_forward_f32", m)) return rc;
     if (rows == 0) return FB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (fb_use_spec(m)) { FB_CUDA(m->spec->forward32(m->p32, rows, X, dead_bits, logits, m->num_sms, st)); return FB_OK; }
@@ -736,6 +852,7 @@ extern "C" int fb_pair_screen(const fb_model *m, int64_t rows, const float *X, i
 {
     if (!m || rows < 0 || !pa_cols_host || (rows > 0 && (!X || !orig_pred || !first_flip)))
         return fb_fail(FB_ERR_INVALID, "fb_pair_screen: bad argument");
+    if (int rc = fb_check_device("fb_pair_screen", m)) return rc;
     if (n_pa < 1 || n_pa > FB_MAX_PA) return fb_fail(FB_ERR_UNSUPPORTED, "fb_pair_screen: %d protected columns (supported: 1..%d)", n_pa, FB_MAX_PA);
     if (k_alts < 0 || (k_alts > 0 && !alts)) return fb_fail(FB_ERR_INVALID, "fb_pair_screen: bad alternatives");
     FbPaCols pa{};
@@ -786,8 +903,7 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
     cudaStream_t st = (cudaStream_t)stream;
     int chunks, chunk_len;
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
-    fb_pool_keep_cached(m->device);
-    DevBuf key(st);
+    DevBuf key(m->device, st);
     FB_CUDA(key.alloc(sizeof(unsigned long long) * n));
     FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
     if (fb_use_spec(m)) {
@@ -938,6 +1054,7 @@ extern "C" int fb_heuristic(const fb_model *m, int64_t n, const double *ws_lb, c
                             uint32_t *merged, void *stream)
 {
     if (!m || n < 0) return fb_fail(FB_ERR_INVALID, "fb_heuristic: bad argument");
+    if (int rc = fb_check_device("fb_heuristic", m)) return rc;
     if (n == 0) return FB_OK;
     if (!ws_lb || !ws_ub || !cand || !s_cand || !deads || !new_deads || !merged)
         return fb_fail(FB_ERR_INVALID, "fb_heuristic: null argument");

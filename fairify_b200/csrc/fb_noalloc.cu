@@ -34,6 +34,7 @@ static std::mutex fb_noalloc_mu;
 static uint32_t *fb_noalloc_ptr[FB_NOALLOC_MAX_DEVICES];      // per-device address of the array above
 
 void fb_set_error(const char *msg);      // fb_api.cu: message returned by fb_last_error()
+extern "C" int fb_model_device(const fb_model *m, int *device);
 
 #define FB_NOALLOC_FAIL(code, ...)                          \
     do {                                                    \
@@ -72,13 +73,18 @@ extern "C" int fb_prune_noalloc(const fb_model *m, int64_t n, const int32_t *box
     if (!m || fb_model_info(m, nullptr, &N, nullptr, nullptr) != FB_OK)
         FB_NOALLOC_FAIL(FB_ERR_INVALID, "fb_prune_noalloc: null model");
     if (n < 0) FB_NOALLOC_FAIL(FB_ERR_INVALID, "fb_prune_noalloc: n = %lld", (long long)n);
-    if ((unsigned long long)n * (unsigned long long)N > FB_NOALLOC_MAX_WORDS)
+    if ((unsigned long long)n > FB_NOALLOC_MAX_WORDS / (unsigned)N)          // (a division: n * N could wrap for huge n)
         FB_NOALLOC_FAIL(FB_ERR_UNSUPPORTED,
-                        "fb_prune_noalloc: %lld partitions x %d neurons = %llu counters exceed the built-in scratch of %u "
+                        "fb_prune_noalloc: %lld partitions x %d neurons exceed the built-in scratch of %u counters "
                         "(at most %u partitions per call for this model); split the batch or use fb_prune",
-                        (long long)n, N, (unsigned long long)n * N, FB_NOALLOC_MAX_WORDS, FB_NOALLOC_MAX_WORDS / (unsigned)N);
+                        (long long)n, N, FB_NOALLOC_MAX_WORDS, FB_NOALLOC_MAX_WORDS / (unsigned)N);
     if (!out) FB_NOALLOC_FAIL(FB_ERR_INVALID, "fb_prune_noalloc: null output block");
     if (n == 0) return FB_OK;
+    // the scratch address below is the current device's copy of the array: it must be the device the model's
+    // weights live on, or kernels on one GPU would be handed a pointer into another
+    int mdev = -1, cur = -1;
+    if (fb_model_device(m, &mdev) != FB_OK || cudaGetDevice(&cur) != cudaSuccess || mdev != cur)
+        FB_NOALLOC_FAIL(FB_ERR_INVALID, "fb_prune_noalloc: the model lives on device %d but device %d is current", mdev, cur);
     uint32_t *counts = nullptr;
     if (int rc = fb_noalloc_scratch_ptr(&counts)) return rc;
     // the two stages of fb_prune, on the built-in scratch; neither allocates (fb_profile zeroes the

@@ -47,6 +47,15 @@ struct FbSpecIbpEntry {
                        const uint32_t *unb, const FbPruneOut *out, int num_sms, cudaStream_t st);
 };
 
+// shape-specialised DMMA profile kernel (fb_mma_spec.cuh): the wide networks
+struct FbMmaNet;
+struct FbSpecMmaEntry {
+    FbSpecShape shape;
+    cudaError_t (*profile)(const FbMmaNet &net, int64_t n, const int32_t *boxes, const int32_t *samples, uint64_t seed,
+                           int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *counts, int num_sms,
+                           cudaStream_t st);
+};
+
 template <class E>
 struct FbSpecTableT {
     const E *entries;
@@ -55,6 +64,8 @@ struct FbSpecTableT {
 typedef FbSpecTableT<FbSpecFwdEntry> FbSpecFwdTable;
 typedef FbSpecTableT<FbSpecProfileEntry> FbSpecProfileTable;
 typedef FbSpecTableT<FbSpecIbpEntry> FbSpecIbpTable;
+typedef FbSpecTableT<FbSpecMmaEntry> FbSpecMmaTable;
+extern const FbSpecMmaTable fb_spec_mma_table_a, fb_spec_mma_table_b, fb_spec_mma_table_c;
 
 // defined in fb_specF_*.cu / fb_specP_*.cu / fb_specI_*.cu
 #define FB_SPEC_DECLARE_TABLES(U)                              \

@@ -16,3 +16,9 @@
 #define FB_SPEC_LIST_f(X) X(13, 64, 32, 16, 8, 4, 1) X(16, 64, 32, 16, 8, 4, 1)
 // GC-5 (20-64-32-16-8-4-1, 4004 weights): fits the kernel-parameter space with float32-stored biases
 #define FB_SPEC_LIST_g(X) X(20, 64, 32, 16, 8, 4, 1)
+
+// Architectures whose activation profile runs on the FP64 matrix instruction with compile-time widths (fb_specM_x.cu):
+// the four wide reference networks ...
+#define FB_SPEC_MMA_LIST_a(X) X(13, 100, 100, 1) X(13, 64, 64, 1)       /* AC-4, AC-5 */
+#define FB_SPEC_MMA_LIST_b(X) X(16, 150, 100, 50, 1)                    /* BM-4 */
+#define FB_SPEC_MMA_LIST_c(X) X(16, 64, 64, 1)                          /* BM-7 */

@@ -74,6 +74,12 @@ int fb_model_create(int L, const int32_t *dims, const float *w_host, const float
 void fb_model_destroy(fb_model *m);
 /* N = neurons, P = weights, specialised = 1 when a compile-time-unrolled kernel set serves this shape */
 int fb_model_info(const fb_model *m, int *L, int *N, int *P, int *specialised);
+/* the device the model's weights live on; every call that takes the model fails unless that device is current */
+int fb_model_device(const fb_model *m, int *device);
+/* fb_prune, fb_prune_host and fb_partition_screen draw their scratch and staging buffers from a memory pool private to
+ * this library (one per device) and keep freed blocks cached there for the next call; this returns the cached memory
+ * to the driver (call it between phases, or before another component needs the whole GPU). */
+int fb_release_cache(void);
 
 /* -- partition grid: utils/input_partition.py:17-46 `partition`, :48-76 `partitioned_ranges` ---- */
 /* lo/hi in column order, T = PARTITION_THRESHOLD, key_order[k] = column index of the k-th range_dict key */

@@ -397,8 +397,56 @@ def singular_cases():
     np.savez_compressed(os.path.join(HERE, "singular_cases.npz"), **out)
 
 
+def sliver_network():
+    """A 13-5-5-1 network (AC-8's shape, Adult columns) whose layer-0 neuron 0 has ws_ub = 2^-50 on the box below: the
+    terms 2^-52 * 4 + 1 * 4 - 4 cancel to within the rounding-error tolerance, so the GPU path must flag the neuron
+    and hand it to Z3."""
+    w0 = np.zeros((13, 5), np.float32); w0[0, 0] = 2.0 ** -52; w0[1, 0] = 1.0; w0[0, 1:] = 1.0; w0[1, 1:] = 0.5
+    b0 = np.array([-4.0, 0.0, 1.0, -1.0, 0.5], np.float32)
+    rng = np.random.RandomState(5)
+    w1 = (rng.standard_normal((5, 5)) * 0.5).astype(np.float32); b1 = (rng.standard_normal(5) * 0.5).astype(np.float32)
+    w2 = rng.standard_normal((5, 1)).astype(np.float32); b2 = np.array([0.1], np.float32)
+    return [w0, w1, w2], [b0, b1, b2]
+
+
+def sliver_case():
+    """The reference's sound_prune (Z3 included) on sliver_network(): python tests/golden/make_golden.py sliver"""
+    ref = refshim.load()
+    P = ref.prune
+    D = domains.DOMAINS["AC"]
+    w32, b32 = sliver_network()
+    w64 = [x.astype(np.float64) for x in w32]; b64 = [x.astype(np.float64) for x in b32]
+    layer_net, _ = refshim.model_functions("AC-8")
+    df = pd.DataFrame(np.zeros((2, D.d + 1)), columns=D.columns + [D.label])
+    p = D.copy_ranges()
+    p["age"] = [0, 4]; p["workclass"] = [0, 4]
+    out = {}
+    S = 6
+    for seed in range(1000):                      # a seed whose samples never activate neuron 0 (needs x1 = 4, x0 >= 1)
+        np.random.seed(seed)
+        with refshim.quiet():
+            bounds, cand, s_cand, b_dead, s_dead, dead, pos_prob, sim_df = P.sound_prune(df, w64, b64, S, layer_net, p)
+        if cand[0][0] == 1:
+            break
+    assert cand[0][0] == 1 and bounds[1][0][0] == 2.0 ** -50 and b_dead[0][0] == 0
+    out["seed"] = np.int64(seed); out["S"] = np.int64(S); out["box"] = box_array(p, D.columns)
+    sim = sim_df.to_numpy()
+    out["sim_sha256"] = np.frombuffer(hashlib.sha256(sim.astype(np.int32).tobytes()).digest(), dtype=np.uint8)
+    for l in range(3):
+        out[f"w{l}"] = w32[l]; out[f"b{l}"] = b32[l]
+    for k, v in (("cand", cand), ("s_cand", s_cand), ("b_dead", b_dead), ("s_dead", s_dead), ("dead", dead)):
+        out[k] = flat_u8(v)
+    for k, v in zip(("ws_lb", "ws_ub", "pl_lb", "pl_ub"), bounds):
+        out[k] = flat(v)
+    out["pos_prob"] = flat(pos_prob)
+    np.savez_compressed(os.path.join(HERE, "sliver_case.npz"), **out)
+    print("sliver case: seed", seed, "cand", flat_u8(cand), "s_dead", flat_u8(s_dead), "dead", flat_u8(dead))
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "singular":
         singular_cases()
+    elif len(sys.argv) > 1 and sys.argv[1] == "sliver":
+        sliver_case()
     else:
         main()

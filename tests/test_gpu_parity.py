@@ -75,7 +75,13 @@ def test_prune_matches_reference_goldens(eng, name):
         boxes = np.stack([c["box"] for c in cs]); samples = np.stack([c["samples"] for c in cs])
         r = m.prune(boxes, samples=samples, tol=tol, want=eng.ALL_OUTPUTS)
         cand, b_dead, dead, sliver = r.bits("cand"), r.bits("b_dead"), r.bits("dead"), r.bits("sliver")
+        s_dead, s_cand = r.bits("s_dead"), r.bits("s_cand")
         counts = r.numpy("counts").view(np.uint16)
+        # where the fixture has no Z3 run, the oracle's closed form (pinned by tests/test_oracle_golden.py) stands in
+        net = O.Net(w, b)
+        om = O.masks(net, np.stack([O.profile(net, c["samples"][None])[0] for c in cs]),
+                     np.stack([c["ws_ub"] for c in cs]), np.stack([c["pl_lb"] for c in cs]),
+                     np.stack([c["pl_ub"] for c in cs]), tol)
         for k, c in enumerate(cs):
             assert np.array_equal(cand[k], c["cand"]), c["tag"]
             assert np.array_equal(counts[k] / S, c["pos_prob"]), c["tag"]
@@ -83,14 +89,69 @@ def test_prune_matches_reference_goldens(eng, name):
             assert not sliver[k].any()
             if "dead" in c:
                 assert np.array_equal(dead[k], c["dead"]), c["tag"]
-            else:
-                assert np.array_equal(dead[k], c["b_dead"]), c["tag"]
+                assert np.array_equal(s_dead[k], c["s_dead"]) and np.array_equal(s_cand[k], c["s_cand"]), c["tag"]
+            assert np.array_equal(dead[k], om["dead"][k]) and np.array_equal(s_dead[k], om["s_dead"][k]), c["tag"]
+            assert np.array_equal(s_cand[k], om["s_cand"][k]), c["tag"]
             for key in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"):
                 assert np.array_equal(r.numpy(key)[k], c[key]), f"{c['tag']} {key}"
             lb_rd, ub_ru = r.numpy("lb_rd")[k], r.numpy("ub_ru")[k]
             assert np.all(lb_rd <= c["ws_lb"]) and np.all(ub_ru >= c["ws_ub"]), c["tag"]
             scale = np.maximum(1.0, np.maximum(np.abs(c["ws_lb"]), np.abs(c["ws_ub"])))
             assert np.all(c["ws_lb"] - lb_rd <= 1e-9 * scale) and np.all(ub_ru - c["ws_ub"] <= 1e-9 * scale)
+
+
+@pytest.mark.parametrize("name", G.singular_models)
+def test_singular_verification_matches_reference_z3(eng, name):
+    """s_dead / s_candidates / dead_nodes of the full sound_prune* INCLUDING the Z3 singular_verification
+    (utils/prune.py:276-644), on the fixtures of every model with an equal-width hidden layer: the device's closed
+    form of the query must reproduce what the unmodified reference + Z3 returned (neurons declared dead although their
+    interval bound is positive included), and the packed record must carry the same masks."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b)
+    tol = _tol(eng, name)
+    cs = list(G.singular_cases(name))
+    boxes = np.stack([c["box"] for c in cs]); samples = np.stack([c["samples"] for c in cs])
+    r = m.prune(boxes, samples=samples, tol=tol, want=eng.ALL_OUTPUTS)
+    rec = r.numpy("record").view(np.uint32)
+    for key in ("cand", "b_dead", "s_dead", "s_cand", "dead"):
+        got = r.bits(key)
+        for k, c in enumerate(cs):
+            assert np.array_equal(got[k], c[key]), f"{c['tag']} {key}"
+    assert not r.bits("sliver").any()
+    assert np.array_equal(r.numpy("ws_ub"), np.stack([c["ws_ub"] for c in cs]))
+    assert np.array_equal(rec[:, 0], r.numpy("verdict").astype(np.uint32))
+    assert np.array_equal(rec[:, 1:1 + m.NW], r.numpy("dead").view(np.uint32))
+    assert np.array_equal(rec[:, 1 + m.NW:1 + 2 * m.NW], r.numpy("cand").view(np.uint32))
+    assert np.all(rec[:, -1] == 0xffffffff)
+    hits = sum(int(c["s_dead"].sum()) for c in cs)
+    if name in ("AC-4", "AC-8", "AC-10", "AC-12", "BM-6", "BM-7"):
+        assert hits > 0 and r.bits("s_dead").sum() == hits
+
+
+def test_sliver_flag_set_by_a_constructed_case(eng):
+    """A network built so that the singular-verification quantity of a hidden neuron lands inside the tolerance: the
+    device must flag it (sliver bit + FB_VERDICT_SLIVER), exactly like the oracle, on layer 0 (quantity = ws_ub) and
+    on a square layer 1 (quantity = q)."""
+    # layer 0 neuron 0 over the box [0,4]x[0,4]: 2^-52 * 4 + 1 * 4 - 4 = 2^-50, far inside the tolerance of sums of
+    # magnitude 8; the other neurons are plainly positive (with a forced tolerance of 1e3 they are all flagged, which
+    # exercises the |q| <= tol test of the square layer 1)
+    w = [np.array([[2.0 ** -52, 1.0], [1.0, 1.0]], np.float32), np.array([[0.5, 0.25], [-0.5, 0.5]], np.float32),
+         np.array([[1.0], [1.0]], np.float32)]
+    b = [np.array([-4.0, 0.0], np.float32), np.array([0.125, -1.0], np.float32), np.array([0.25], np.float32)]
+    m = eng.Model(w, b); net = O.Net(w, b)
+    box = np.array([[[0, 4], [0, 4]]], dtype=np.int32)
+    tol = eng.sliver_tolerance(w, b, box[0, :, 0], box[0, :, 1])
+    assert np.array_equal(tol, O.sliver_tolerance(net, box[0, :, 0], box[0, :, 1]))
+    for force_tol in (tol, np.full_like(tol, 1e3)):          # the honest tolerance, then one that flags every candidate
+        r = m.ibp(box, tol=force_tol, want=eng.ALL_OUTPUTS)
+        _, ws_ub, pl_lb, pl_ub = O.ibp(net, box)
+        om = O.masks(net, None, ws_ub, pl_lb, pl_ub, force_tol)
+        for key in ("cand", "b_dead", "s_dead", "s_cand", "dead", "sliver"):
+            assert np.array_equal(r.bits(key), om[key]), key
+        assert bool(r.numpy("verdict")[0] & eng.VERDICT_SLIVER) == bool(om["sliver"].any())
+    assert om["sliver"].any()
+    r = m.ibp(box, tol=tol, want=("sliver",))
+    assert r.bits("sliver")[0][0] == 1 and r.bits("sliver").sum() == 1      # layer 0 neuron 0: 0 < ws_ub = 2^-50 <= tol
 
 
 @pytest.mark.parametrize("name", MODELS)
@@ -116,6 +177,7 @@ def test_prune_matches_oracle_philox(eng, name):
     assert np.array_equal(r.bits("cand"), want["cand"])
     assert np.array_equal(r.bits("b_dead"), want["b_dead"])
     assert np.array_equal(r.bits("dead"), want["dead"])
+    assert np.array_equal(r.bits("s_dead"), want["s_dead"])
     assert np.array_equal(r.bits("sliver"), want["sliver"])
     assert np.array_equal(r.numpy("verdict"), want["verdict"])
     o_rn = O.ibp(net, hb); o_dir = O.ibp_directed(net, hb)
@@ -216,11 +278,16 @@ def test_subnormal_capable_model_takes_exact_sign_test(eng):
     assert want[:, 40:45].all()                # the last hidden layer is active with values below 2^-1042
 
 
-@pytest.mark.parametrize("name,tiled", [("AC-1", "1"), ("AC-12", "1"), ("GC-2", "1"), ("BM-1", "1"), ("AC-1", "0"),
-                                        ("BM-1", "0"), ("BM-4", "0"), ("AC-5", "0")])
-def test_generic_kernels_agree_with_specialised(eng, name, tiled):
+@pytest.mark.parametrize("name,tiled,mma", [
+    ("AC-1", "1", "1"), ("AC-12", "1", "1"), ("GC-2", "1", "1"), ("BM-1", "1", "1"), ("GC-5", "1", "1"), ("AC-7", "1", "1"),
+    ("GC-3", "1", "1"), ("AC-9", "1", "1"), ("BM-4", "1", "1"), ("AC-4", "1", "1"), ("BM-7", "1", "1"),
+    ("AC-1", "1", "0"), ("BM-1", "1", "0"), ("BM-4", "1", "0"), ("AC-5", "1", "0"),
+    ("AC-1", "0", "0"), ("BM-1", "0", "0"), ("BM-4", "0", "0"), ("AC-5", "0", "0"), ("AC-10", "0", "0"), ("AC-8", "0", "0"),
+    ("BM-6", "0", "0")])
+def test_generic_kernels_agree_with_specialised(eng, name, tiled, mma):
     """FAIRIFY_B200_FORCE_GENERIC routes a specialised shape through the runtime-shape kernels (subprocess); the profile
-    goes through the tiled kernel, or with FAIRIFY_B200_TILED_PROFILE=0 through the sample-per-lane kernel."""
+    goes through the DMMA kernel (FAIRIFY_B200_MMA_PROFILE=1), the older tiled kernel (=0 with
+    FAIRIFY_B200_TILED_PROFILE=1) or the sample-per-lane kernel (both 0)."""
     import subprocess
     import sys
     code = f"""
@@ -238,6 +305,15 @@ r = m.prune(boxes, S=77, seed=3, tol=tol, want=engine.ALL_OUTPUTS)
 want = O.prune_batch(net, hb, 3, 0, 77, tol)
 assert np.array_equal(r.numpy('counts').view(np.uint16), want['counts'].astype(np.uint16))
 assert np.array_equal(r.bits('b_dead'), want['b_dead']) and np.array_equal(r.numpy('verdict'), want['verdict'])
+assert np.array_equal(r.bits('s_dead'), want['s_dead']) and np.array_equal(r.bits('dead'), want['dead'])
+if {name!r} in G.singular_models:
+    cs = list(G.singular_cases({name!r}))
+    rs = m.prune(np.stack([c['box'] for c in cs]), samples=np.stack([c['samples'] for c in cs]), tol=tol, want=engine.ALL_OUTPUTS)
+    for key in ('cand', 'b_dead', 's_dead', 's_cand', 'dead'):
+        assert np.array_equal(rs.bits(key), np.stack([c[key] for c in cs])), key
+    rec = rs.numpy('record').view(np.uint32)
+    assert np.array_equal(rec[:, 1:1 + m.NW], rs.numpy('dead').view(np.uint32)) and np.all(rec[:, -1] == 0xffffffff)
+    assert np.array_equal(rec[:, 0], rs.numpy('verdict').astype(np.uint32))
 assert np.array_equal(r.numpy('ws_ub'), O.ibp(net, hb)[1]) and np.array_equal(r.numpy('ub_ru'), O.ibp_directed(net, hb)[1])
 X = O.philox_samples(3, 0, hb, 8).reshape(-1, m.d)
 assert np.array_equal(m.forward(X.astype(np.float64)).cpu().numpy(), O.forward_f64(net, X))
@@ -247,7 +323,7 @@ ce = m.partition_screen(boxes, pa, S=77, seed=3)[0].cpu().numpy()
 assert np.array_equal(ce, O.partition_screen(net, O.philox_samples(3, 0, hb, 77), hb, pa)[0])
 print('generic-ok', m.specialised)
 """
-    env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1", FAIRIFY_B200_TILED_PROFILE=tiled)
+    env = dict(os.environ, FAIRIFY_B200_FORCE_GENERIC="1", FAIRIFY_B200_TILED_PROFILE=tiled, FAIRIFY_B200_MMA_PROFILE=mma)
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "generic-ok" in out.stdout, out.stdout + out.stderr
 

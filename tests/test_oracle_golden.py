@@ -260,3 +260,22 @@ def test_point_to_partition_density(tag):
     # non-integer points between two chunks belong to no partition
     Xf = X[inside][:5].astype(np.float64); Xf[:, 0] = 39.5 if int(z[f"{tag}/T"]) == 30 else 21.5
     assert np.all(O.grid_locate(lo, hi, int(z[f"{tag}/T"]), ko, Xf) == -1)
+
+
+def test_constructed_sliver_case_is_flagged():
+    """tests/golden/sliver_case.npz: the reference (with Z3) on a network built so that ws_ub of layer-0 neuron 0 is
+    2^-50 -- inside the rounding tolerance.  The oracle must flag exactly that neuron and otherwise agree."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "sliver_case.npz"))
+    w = [z[f"w{l}"] for l in range(3)]; b = [z[f"b{l}"] for l in range(3)]
+    net = O.Net(w, b)
+    from tests.common import reference_samples
+    box = z["box"]
+    samples = reference_samples(z["seed"], box, z["S"])
+    assert hashlib.sha256(samples.tobytes()).digest() == z["sim_sha256"].tobytes()
+    tol = O.sliver_tolerance(net, box[:, 0], box[:, 1])
+    _, ws_ub, pl_lb, pl_ub = O.ibp(net, box[None])
+    assert np.array_equal(ws_ub[0], z["ws_ub"]) and ws_ub[0][0] == 2.0 ** -50
+    m = O.masks(net, O.profile(net, samples[None]), ws_ub, pl_lb, pl_ub, tol)
+    assert m["sliver"][0][0] == 1 and m["sliver"][0].sum() == 1
+    for k in ("cand", "b_dead", "s_dead", "s_cand", "dead"):
+        assert np.array_equal(m[k][0], z[k]), k

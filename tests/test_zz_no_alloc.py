@@ -94,3 +94,43 @@ def test_noalloc_runtime_shape_model_and_limit():
     n_ok = NOALLOC_MAX_WORDS // m.N
     rc, out = _call("fb_prune_noalloc", m, boxes[:n_ok], 8, 1, 0, tol, ("verdict",))
     assert rc == 0 and not np.any(out["verdict"] == 255)
+
+
+def test_noalloc_call_allocates_nothing():
+    """After a warm-up call (which resolves the scratch array's address), a call must leave the device's free memory
+    and the default stream-ordered pool exactly as they were -- fb_prune, by contrast, grows this library's pool."""
+    from fairify_b200 import _lib, engine
+    cudart = C.CDLL("libcudart.so.12") if hasattr(C, "CDLL") else None
+    dom = G.domain("AC-1")
+    m = engine.Model(*G.wb("AC-1"))
+    grid = engine.Grid(dom.columns, dom.ranges, 10)
+    tol = _tol(m, "AC-1")
+    boxes = grid.boxes(0, 12000)
+    want = ("cand", "b_dead", "dead", "verdict")
+    outs, po = m._alloc_outputs(boxes.shape[0], want)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def call():
+        rc = _lib.lib().fb_prune_noalloc(m._h, boxes.shape[0], C.c_void_p(boxes.data_ptr()), None, 64, C.c_uint64(5), 0,
+                                         C.c_void_p(tol.data_ptr()), C.byref(po), st)
+        torch.cuda.synchronize()
+        return rc
+
+    def pool_bytes():
+        pool = C.c_void_p()
+        assert cudart.cudaDeviceGetDefaultMemPool(C.byref(pool), torch.cuda.current_device()) == 0
+        used, reserved = C.c_uint64(), C.c_uint64()
+        # cudaMemPoolAttrReservedMemCurrent = 5, cudaMemPoolAttrUsedMemCurrent = 7
+        assert cudart.cudaMemPoolGetAttribute(pool, 5, C.byref(reserved)) == 0
+        assert cudart.cudaMemPoolGetAttribute(pool, 7, C.byref(used)) == 0
+        return used.value, reserved.value
+
+    assert call() == 0                                  # warm-up: address lookup, module load
+    free0 = torch.cuda.mem_get_info()[0]; pool0 = pool_bytes()
+    for _ in range(3):
+        assert call() == 0
+    assert torch.cuda.mem_get_info()[0] == free0 and pool_bytes() == pool0
+    # a model on another device than the current one is refused (the scratch address belongs to the current device)
+    if torch.cuda.device_count() > 1:
+        with torch.cuda.device(1):
+            assert call() != 0 and b"device" in _lib.lib().fb_last_error()

@@ -1,4 +1,5 @@
 """Model cache and thin helpers between the reference-shaped API and fairify_b200.engine."""
+import collections
 import hashlib
 
 import numpy as np
@@ -24,14 +25,44 @@ def model_for(w, b):
     return m
 
 
+# Pruned networks.  The drivers call prune_neurons() once per partition and then predict with the compacted weights
+# (get_y_pred on the 1000 samples, the C-check: src/AC/Verify-AC.py:229-274).  Compaction only deletes terms that are
+# zero anyway, so the pruned network equals the original one with the dead neurons' activations forced to 0 -- which
+# fb_forward_* does with a mask on the resident model.  prune_neurons registers its result here (the arrays are kept
+# alive while registered, so their ids cannot be reused); logits() recognises them.
+_pruned = collections.OrderedDict()
+_PRUNED_KEEP = 8
+
+
+def remember_pruned(pr_w, pr_b, weight, bias, dead_lists):
+    key = tuple(id(a) for a in pr_w) + tuple(id(a) for a in pr_b)
+    mask = np.concatenate([np.asarray(l, dtype=np.uint8) != 0 for l in dead_lists]).astype(np.uint8)
+    _pruned[key] = (list(pr_w), list(pr_b), list(weight), list(bias), mask)
+    while len(_pruned) > _PRUNED_KEEP:
+        _pruned.popitem(last=False)
+
+
+def _as_pruned(w, b):
+    """(original model, dead mask words) when (w, b) is a registered prune_neurons result, else None."""
+    hit = _pruned.get(tuple(id(a) for a in w) + tuple(id(a) for a in b))
+    if hit is None:
+        return None
+    _, _, weight, bias, mask = hit
+    m = model_for(weight, bias)
+    return m, engine.pack_bits(mask[None])[0]
+
+
 def logits(X, w, b):
     """numpy logits for rows X: float32 when both X and the weights are float32 (numpy's promotion in
     `w.T @ x`), float64 otherwise."""
     X = np.asarray(X)
     f32 = X.dtype == np.float32 and all(np.asarray(a).dtype == np.float32 for a in w)
-    m = model_for(w, b)
-    out = m.forward(X.astype(np.float32 if f32 else np.float64))
-    return out.cpu().numpy()
+    X = X.astype(np.float32 if f32 else np.float64)
+    pruned = _as_pruned(w, b)
+    if pruned is not None:
+        m, dead_bits = pruned
+        return m.forward(X, dead_bits=dead_bits).cpu().numpy()
+    return model_for(w, b).forward(X).cpu().numpy()
 
 
 def layer_activations(x, w, b):

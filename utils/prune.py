@@ -9,13 +9,22 @@ pandas `sim_df`), so `from utils.prune import *` keeps the unchanged drivers wor
 What runs where
   * sampling keeps the reference's RNG: `np.random.randint(lo, hi+1, size=(S, d))` consumes the global legacy
     stream exactly like the scalar loop of `simluate_data` (utils/prune.py:205-222) -- same seed, same samples;
-  * activation profile, interval bounds, masks, keep-one fixes, merge: one `fb_prune` call on the device
-    (`candidate_dead_nodes` :168-192, `neuron_bounds` :105-164, `dead_node_from_bound` :226-251, :689-705);
-  * the per-neuron Z3 query (`singular_verification*`, :276-644) stays on the host.  It asks whether
-    y_j > 0 is satisfiable over the layer's input box; the device already knows the supremum of y_j over that
-    box (it is ws_ub), so the query is only run for neurons whose bound is within rounding error of zero
-    ("slivers").  FAIRIFY_GPU_SINGULAR=reference runs it for every remaining candidate like the reference,
-    =off never runs it.  s_dead is all-zero in every published result and every fixture.
+  * activation profile, interval bounds, masks, singular verification, keep-one fixes, merge: one `fb_prune` call on
+    the device (`candidate_dead_nodes` :168-192, `neuron_bounds` :105-164, `dead_node_from_bound` :226-251,
+    `singular_verification*` :276-644, :689-705);
+  * the per-neuron Z3 query of `singular_verification*` is answered on the device from the closed form of what the
+    reference asks (for a hidden layer l >= 1 it boxes the layer's inputs with the layer's OWN post-activation bounds,
+    :266-273 called with layer_index at :302-345 -- see include/fairify_b200.h, fb_ibp).  Only neurons whose
+    float result is within rounding error of zero ("slivers") go to Z3 on the host.  FAIRIFY_GPU_SINGULAR=reference
+    runs the host query for every remaining candidate like the reference, =off never runs it;
+  * batching behind the unbatched API: when `range_dict` is a PartitionBox of a PartitionList
+    (utils/input_partition.py), the call computes a whole WINDOW of the list -- the next FAIRIFY_GPU_WINDOW (4096)
+    partitions in the list's current order, so `shuffle(p_list)` is honoured -- in one launch and serves the following
+    calls from it.  The samples of the window are drawn partition by partition from the global numpy stream and the
+    stream state is put back to where the reference would have left it after every served call; a window is dropped
+    as soon as the caller does anything the window did not foresee (another partition order, another model, random
+    draws of its own in between), so results and RNG consumption are those of the one-at-a-time path
+    (FAIRIFY_GPU_WINDOW=1);
   * `heuristic_prune` (:862-939) runs on the device too (`fb_heuristic`);
   * `prune_neurons`, `compression_ratio`, `merge_dead_nodes` operate on a handful of Python lists per
     partition and feed Z3; they stay host code.
@@ -118,7 +127,10 @@ def merge_dead_nodes(b, s):
 
 
 def prune_neurons(weight, bias, candidates):
-    """Delete dead columns / the next layer's rows (reference :950-977); feeds the Z3 encoder on the host."""
+    """Delete dead columns / the next layer's rows (reference :950-977); feeds the Z3 encoder on the host.
+    The result is remembered as "these weights with that mask", so that predictions with the pruned network
+    (`get_y_pred(net, pr_w, pr_b, ...)`, the C-check) run on the resident original model with the dead neurons
+    masked instead of uploading a new model per partition."""
     pr_w, pr_b = [], []
     keep_prev = None
     for i in range(len(weight)):
@@ -128,6 +140,7 @@ def prune_neurons(weight, bias, candidates):
             wi = wi[keep_prev, :]
         pr_w.append(wi[:, keep]); pr_b.append(np.asarray(bias[i])[keep])
         keep_prev = keep
+    _device.remember_pruned(pr_w, pr_b, weight, bias, candidates)
     print('Pruning done!')
     return pr_w, pr_b
 
@@ -160,19 +173,27 @@ def _z3_positive_is_unsat(l, j, cols, weight, bias, ranges, pl_lb, pl_ub):
     return s.check() == z3.unsat
 
 
-def _singular(cand, df, weight, bias, ranges, pl_lb, pl_ub, only=None):
+def _singular(cand, df, weight, bias, ranges, pl_lb, pl_ub, only=None, otherwise=None):
+    """The reference's loop (:276-356).  `only` restricts the Z3 query to the flagged neurons; the others take
+    their answer from `otherwise` (the device's closed form)."""
     print('SINGULAR VERIFICATION')
     candidates = copy.deepcopy(cand)
     dead = copy.deepcopy(cand)
     cols = list(df.columns.values)
     finds = total = 0
     for l in range(len(candidates) - 1):
+        if l >= 1 and any(candidates[l]) and len(candidates[l]) > np.asarray(weight[l]).shape[0]:
+            raise IndexError("index %d is out of bounds for axis 0 with size %d" %
+                             (np.asarray(weight[l]).shape[0], np.asarray(weight[l]).shape[0]))   # as the reference (:269-270)
         for j in range(len(candidates[l])):
             total += 1
             if candidates[l][j] == 0:
                 continue
-            run = only is None or only[l][j]
-            if run and _z3_positive_is_unsat(l, j, cols, weight, bias, ranges, pl_lb, pl_ub):
+            if only is None or only[l][j]:
+                unsat = _z3_positive_is_unsat(l, j, cols, weight, bias, ranges, pl_lb, pl_ub)
+            else:
+                unsat = bool(otherwise[l][j]) if otherwise is not None else False
+            if unsat:
                 finds += 1; dead[l][j] = 1; candidates[l][j] = 0
             else:
                 dead[l][j] = 0
@@ -190,39 +211,113 @@ singular_verification_compass = singular_verification_default = singular_verific
 # ----------------------------------------------------------------------------------------------------
 # sound_prune*: the drop-in entry points (reference :671-859; they differ only in the label column)
 # ----------------------------------------------------------------------------------------------------
+_WANT = ("cand", "b_dead", "dead", "sliver", "s_dead", "s_cand", "counts", "ws_lb", "ws_ub", "pl_lb", "pl_ub")
+
+
+class _Window:
+    """Results of one batched launch: `items[k]` is the PartitionBox served k-th."""
+
+    def __init__(self, key, items, sims, states, arrays):
+        self.key, self.items, self.sims, self.states, self.arrays = key, items, sims, states, arrays
+        self.next = 0
+
+
+_window = None
+
+
+def _same_rng_state(a, b):
+    return a[2] == b[2] and a[3] == b[3] and a[4] == b[4] and np.array_equal(a[1], b[1])
+
+
+def _window_size():
+    try:
+        return max(1, int(os.environ.get("FAIRIFY_GPU_WINDOW", "4096")))
+    except ValueError:
+        return 4096
+
+
+def _compute(m, cols, boxes, S):
+    """Draw the samples of `boxes` (a list of {attr: [lo, hi]}) one partition after the other from the global numpy
+    stream, run the stage for all of them in one launch, bring everything the 8-tuple needs to the host."""
+    n, d = len(boxes), len(cols)
+    box = np.empty((n, d, 2), dtype=np.int32)
+    sims = np.empty((n, S, d), dtype=np.int64)
+    states = []
+    for k, rd in enumerate(boxes):
+        box[k] = _box_from(cols, rd)
+        sims[k] = np.random.randint(box[k, :, 0].astype(np.int64), box[k, :, 1].astype(np.int64) + 1, size=(S, d))
+        states.append(np.random.get_state())
+    lo, hi = box[:, :, 0].min(axis=0), box[:, :, 1].max(axis=0)
+    tol = m.tolerance(lo, hi)
+    r = m.prune(box, samples=sims.astype(np.int32), tol=tol, want=_WANT)
+    arrays = {k: r.numpy(k) for k in ("ws_lb", "ws_ub", "pl_lb", "pl_ub")}
+    arrays["counts"] = r.numpy("counts").view(np.uint16)
+    for k in ("cand", "b_dead", "dead", "sliver", "s_dead", "s_cand"):
+        arrays[k] = r.bits(k)
+    return sims, states, arrays
+
+
 def _sound_prune(label_name, df, weight, bias, simulation_size, layer_net, range_dict):
+    global _window
     x_df = df.drop(labels=[label_name], axis=1, inplace=False)
     cols = x_df.columns.values
-    sim_df = simluate_data(x_df, simulation_size, range_dict)
     m = _device.model_for(weight, bias)
-    box = _box_from(cols, range_dict)
-    tol = m.tolerance(box[:, 0], box[:, 1])
-    r = m.prune(box[None], samples=sim_df.to_numpy().astype(np.int32)[None], tol=tol,
-                want=("cand", "b_dead", "dead", "sliver", "verdict", "counts", "ws_lb", "ws_ub", "pl_lb", "pl_ub"))
-    bounds = tuple(_split_lists(m, r.numpy(k)[0], float) for k in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"))
-    counts = r.numpy("counts").view(np.uint16)[0]
-    cand_flat = r.bits("cand")[0]
-    candidates = _split_lists(m, cand_flat, int)
-    pos_prob = _split_lists(m, counts / simulation_size, float)
-    b_dead = _split_lists(m, r.bits("b_dead")[0], int)
-    print('INTERVAL BASED PRUNING')
-    # b_candidates: candidates not proven dead by the bound; last layer copied through (:235-251)
-    le0 = np.asarray(r.numpy("ws_ub")[0]) <= 0
-    b_cand_flat = cand_flat & ~le0
-    b_cand_flat[m.boff[m.L - 1]:] = cand_flat[m.boff[m.L - 1]:]
-    b_cand = _split_lists(m, b_cand_flat, int)
+    S = int(simulation_size)
+    key = (id(m), S, tuple(cols))
+    plist = getattr(range_dict, "grid_ref", None)
+    w = _window
+    # the window serves this call only if it is the call the window expects next AND nobody else has drawn from numpy's
+    # global stream since the previous call (the window's samples were drawn assuming nobody would)
+    if not (w is not None and w.key == key and w.next < len(w.items) and w.items[w.next] is range_dict
+            and _same_rng_state(np.random.get_state(), w.states[w.next - 1])):
+        # a new window: the next partitions of the list in its current order, starting at this one
+        items = [range_dict]
+        wsize = _window_size()
+        if plist is not None and wsize > 1:
+            pos = plist.position(range_dict)
+            if pos is not None:
+                items = plist[pos:pos + wsize]
+        sims, states, arrays = _compute(m, cols, items, S)
+        w = _window = _Window(key, items, sims, states, arrays)
+    k = w.next
+    w.next += 1
+    np.random.set_state(w.states[k])           # the global stream is where the reference would have left it
+    a = {name: arr[k] for name, arr in w.arrays.items()}
+    sim_df = pd.DataFrame(data=w.sims[k], columns=cols)
+    if w.next >= len(w.items):
+        _window = None
 
-    mode = os.environ.get("FAIRIFY_GPU_SINGULAR", "sliver")
-    sliver = _split_lists(m, r.bits("sliver")[0], int)
+    bounds = tuple(_split_lists(m, a[name], float) for name in ("ws_lb", "ws_ub", "pl_lb", "pl_ub"))
+    candidates = _split_lists(m, a["cand"], int)
+    pos_prob = _split_lists(m, a["counts"] / simulation_size, float)
+    b_dead = _split_lists(m, a["b_dead"], int)
+    print('INTERVAL BASED PRUNING')
+    mode = os.environ.get("FAIRIFY_GPU_SINGULAR", "device")
+    if mode == "device" and not a["sliver"].any():
+        print('SINGULAR VERIFICATION')
+        s_cand = _split_lists(m, a["s_cand"], int)
+        s_dead = _split_lists(m, a["s_dead"], int)
+        dead_nodes = _split_lists(m, a["dead"], int)
+        return bounds, candidates, s_cand, b_dead, s_dead, dead_nodes, pos_prob, sim_df
+
+    # b_candidates: candidates not proven dead by the bound; last layer copied through (:235-251)
+    le0 = a["ws_ub"] <= 0
+    b_cand_flat = a["cand"] & ~le0
+    b_cand_flat[m.boff[m.L - 1]:] = a["cand"][m.boff[m.L - 1]:]
+    b_cand = _split_lists(m, b_cand_flat, int)
     if mode == "reference":
         s_dead, s_cand, _ = _singular(b_cand, x_df, weight, bias, range_dict, bounds[2], bounds[3])
-    elif mode != "off" and any(any(l) for l in sliver):
-        s_dead, s_cand, _ = _singular(b_cand, x_df, weight, bias, range_dict, bounds[2], bounds[3], only=sliver)
-    else:
+    elif mode == "off":
         print('SINGULAR VERIFICATION')
         s_cand = copy.deepcopy(b_cand)
         s_dead = [[0] * len(l) for l in b_cand]
         s_dead[-1] = list(b_cand[-1])           # the reference copies the last layer through (:287-288)
+    else:
+        # the device's answer everywhere except on the slivers, which get the reference's exact query
+        sliver = _split_lists(m, a["sliver"], int)
+        raw_dead = _split_lists(m, b_cand_flat & ~a["s_cand"], int)       # s_dead before its keep-one fix
+        s_dead, s_cand, _ = _singular(b_cand, x_df, weight, bias, range_dict, bounds[2], bounds[3], only=sliver,
+                                      otherwise=raw_dead)
     _keep_one(s_dead)
     dead_nodes = _keep_one(merge_dead_nodes(b_dead, s_dead))
     return bounds, candidates, s_cand, b_dead, s_dead, dead_nodes, pos_prob, sim_df

@@ -86,5 +86,36 @@ def load_model(path):
     return _KerasLikeModel(w, b)
 
 
+def _tolerant_arity(loader):
+    """The fork's loaders return (df, X_train, y_train, X_test, y_test, encoders) -- utils/verif_utils.py:190, :241,
+    :366 -- while the src/, stress/, relaxed/ and targeted/ drivers still unpack five values (src/GC/Verify-GC.py:23,
+    src/AC/Verify-AC.py:28, src/BM/Verify-BM.py:15) and the -experiment drivers six.  The wrapped loader looks at the
+    caller's next instruction: when it unpacks n < len(result) values it gets the first n."""
+    import dis
+    import functools
+    import sys
+
+    @functools.wraps(loader)
+    def wrapped(*args, **kwargs):
+        out = loader(*args, **kwargs)
+        if not isinstance(out, tuple):
+            return out
+        frame = sys._getframe(1)
+        want = None
+        for ins in dis.get_instructions(frame.f_code):
+            if ins.offset > frame.f_lasti:
+                if ins.opname == "UNPACK_SEQUENCE":
+                    want = ins.argval
+                break
+        if want is not None and want < len(out):
+            return out[:want]
+        return out
+    return wrapped
+
+
 # host-side names that are not on the GPU path: taken from the reference checkout when there is one
 _reference.reexport("verif_utils", globals(), skip=("load_model",))
+for _name in ("load_adult_ac1", "load_german", "load_bank", "load_compass", "load_default", "load_adult", "load_adult_adf"):
+    if _name in globals():
+        globals()[_name] = _tolerant_arity(globals()[_name])
+del _name
