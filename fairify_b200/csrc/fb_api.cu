@@ -129,7 +129,7 @@ static const E *fb_find_spec(const FbSpecTableT<E> *const (&tables)[NT], int L, 
 static const FbSpecFwdTable *const fb_fwd_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_F)};
 static const FbSpecProfileTable *const fb_profile_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_P)};
 static const FbSpecIbpTable *const fb_ibp_tables[] = {FB_SPEC_FOR_EACH_UNIT(FB_TAB_I)};
-static const FbSpecMmaTable *const fb_mma_tables[] = {&fb_spec_mma_table_a, &fb_spec_mma_table_b, &fb_spec_mma_table_c};
+static const FbSpecMmaTable *const fb_mma_tables[] = {&fb_spec_mma_table_a, &fb_spec_mma_table_b, &fb_spec_mma_table_c, &fb_spec_mma_table_d};
 
 extern "C" void fb_model_destroy(fb_model *m)
 {
@@ -611,17 +611,22 @@ extern "C" int fb_profile(const fb_model *m, int64_t n, const int32_t *boxes, co
     int chunks, chunk_len;
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
     if (chunks > 1) FB_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n * m->gen.N, st));
+    // 1. shape-specialised DMMA kernel (the wide and mid-size reference networks; FAIRIFY_B200_MMA_PROFILE=0 turns the
+    //    DMMA kernels off, FAIRIFY_B200_FORCE_GENERIC=1 the shape-specialised ones: tests, comparisons)
+    // 2. shape-specialised FMA kernel (the small networks)   3. runtime-shape DMMA kernel   4. the older runtime-shape kernels
+    static const int mma_env = [] { const char *v = getenv("FAIRIFY_B200_MMA_PROFILE"); return !v ? -1 : (v[0] == '0' ? 0 : 1); }();
+    static const bool force_generic = [] { const char *v = getenv("FAIRIFY_B200_FORCE_GENERIC"); return v && v[0] == '1'; }();
+    if (m->spec_mma && mma_env != 0 && !force_generic) {
+        FB_CUDA(m->spec_mma->profile(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
+        return FB_OK;
+    }
     if (fb_use_spec(m)) {
         FB_CUDA(m->spec_profile->profile(m->p64, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks, chunk_len,
-                                 counts, m->num_sms, st));
+                                         counts, m->num_sms, st));
         return FB_OK;
     }
     if (fb_use_mma_profile(m)) {
-        static const bool generic_mma = [] { const char *v = getenv("FAIRIFY_B200_MMA_GENERIC"); return v && v[0] == '1'; }();
-        if (m->spec_mma && !generic_mma)
-            FB_CUDA(m->spec_mma->profile(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
-        else
-            FB_CUDA(fb_profile_mma(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
+        FB_CUDA(fb_profile_mma(m->mma, n, boxes, samples, seed, first_index, S, chunks, chunk_len, counts, m->num_sms, st));
         return FB_OK;
     }
     if (fb_use_tiled_profile(m)) return fb_profile_tiled(m, n, boxes, samples, S, seed, first_index, counts, chunks > 1, st);

@@ -23,6 +23,11 @@ template <class S> __host__ __device__ constexpr int fb_mma_bpoff(int l)
 }
 
 // Layer l and everything after it.  hin[ms][i][e] = input block 2i+e of the layer (see fb_mma.cuh).
+// (ptxas re-sorts the unrolled matrix instructions of a column group tile by tile -- one accumulator live at a time, each
+//  tile a chain of dependent DMMAs -- whatever order they are written in.  Forcing all tiles to advance together (a
+//  never-taken run-time exit per input block, which pins the written order) was measured on B200: it costs 20
+//  registers, which for the 64-wide networks is the second resident CTA, and loses 6-9 points; with 16 warps per SM the
+//  serial chains are covered by the other warps.)
 template <class S, int l, int MS, int NBIN>
 __device__ __forceinline__ void fb_mma_spec_layers(const double *sW, const double *sB, uint32_t *sCnt,
                                                    const double (&hin)[MS][NBIN][2], const FbMmaLane &ln, int lane,
@@ -109,12 +114,18 @@ __device__ __forceinline__ void fb_mma_spec_layers(const double *sW, const doubl
     if constexpr (!LOGIT) fb_mma_spec_layers<S, l + 1, MS, NB>(sW, sB, sCnt, hout, ln, lane, live);
 }
 
-#ifndef FB_MMA_SPEC_MINB
-#define FB_MMA_SPEC_MINB 1
-#endif
+// widest layer of S in neuron tiles
+template <class S> __host__ __device__ constexpr int fb_mma_maxnb()
+{
+    int r = 0;
+    for (int l = 0; l < S::NL; ++l) r = fb_mma_nb<S>(l) > r ? fb_mma_nb<S>(l) : r;
+    return r;
+}
 
+// two CTAs per SM (registers capped at 128) for one sample block of a network up to 64 wide: the matrix-instruction
+// stream of a warp has gaps (bias / sign / count epilogues, sample generation) that only other resident warps fill
 template <class S, int MS, bool PHILOX>
-__global__ void __launch_bounds__(FB_MMA_WARPS * 32, FB_MMA_SPEC_MINB)
+__global__ void __launch_bounds__(FB_MMA_WARPS * 32, (MS == 1 && fb_mma_maxnb<S>() <= 8) ? 2 : 1)
 fb_profile_mma_spec_kernel(const FbMmaNet net, int64_t n, const int32_t *__restrict__ boxes,
                            const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp, int chunks,
                            int chunk_len, uint32_t *__restrict__ counts)

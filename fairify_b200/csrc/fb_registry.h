@@ -65,7 +65,7 @@ typedef FbSpecTableT<FbSpecFwdEntry> FbSpecFwdTable;
 typedef FbSpecTableT<FbSpecProfileEntry> FbSpecProfileTable;
 typedef FbSpecTableT<FbSpecIbpEntry> FbSpecIbpTable;
 typedef FbSpecTableT<FbSpecMmaEntry> FbSpecMmaTable;
-extern const FbSpecMmaTable fb_spec_mma_table_a, fb_spec_mma_table_b, fb_spec_mma_table_c;
+extern const FbSpecMmaTable fb_spec_mma_table_a, fb_spec_mma_table_b, fb_spec_mma_table_c, fb_spec_mma_table_d;
 
 // defined in fb_specF_*.cu / fb_specP_*.cu / fb_specI_*.cu
 #define FB_SPEC_DECLARE_TABLES(U)                              \

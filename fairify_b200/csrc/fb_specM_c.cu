@@ -1,5 +1,5 @@
 // DMMA profile kernels of the architectures in FB_SPEC_MMA_LIST_c (fb_spec_lists.h)
-#define FB_MMA_SPEC_HAS_MS2 1
+#define FB_MMA_SPEC_MS_MASK 3
 #define FB_MMA_SPEC_DEFAULT_MS 1
 #include "fb_spec_ops_mma.cuh"
 #include "fb_spec_lists.h"

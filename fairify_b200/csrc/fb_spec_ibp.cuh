@@ -239,3 +239,201 @@ fb_ibp_spec_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// The same recurrence with the neuron loop left as a LOOP.
+//
+// fb_ibp_spec_kernel above is one straight line of ~23 instructions per weight (AC-1: 8 000 instructions, 127 KB):
+// it does not fit the instruction cache, and with four bound arrays of two layers live it needs more than 255
+// registers (ncu on B200, AC-1: "no instruction" is the top stall, 1 warp per scheduler, 22 % of the FP64 pipe).
+// Here only the loop over a neuron's INPUTS is unrolled -- the inputs' bounds sit in registers under compile-time
+// indices -- while the neurons of a layer are visited by a run-time loop: the weight is fetched from the constant
+// bank at a run-time offset, the finished neuron's post-activation bounds go to this thread's column of a small
+// shared-memory array, and the next layer reads them back into registers.  Code is ~20 instructions per INPUT of a
+// layer (AC-1: under 1 000 in all), live state 4 x (widest input) doubles.  Masks are kept per layer as 64-bit words
+// (bit j = neuron j), which makes the keep-one fixes single comparisons, and merged into the output words at the end
+// of the layer.  Same arithmetic, same outputs as the unrolled kernel.  For shapes whose hidden layers are at most
+// FB_IBP_LOOP_MAXW wide.
+// ---------------------------------------------------------------------------------------------------
+#define FB_IBP_LOOP_MAXW 16
+#define FB_IBP_LOOP_THREADS 128
+
+template <class S> __host__ __device__ constexpr int fb_ibp_max_hidden()
+{
+    int r = 0;
+    for (int l = 1; l < S::NL; ++l) r = S::dim(l) > r ? S::dim(l) : r;      // inputs of layers 1 .. (hidden widths)
+    return r;
+}
+template <class S> __host__ __device__ constexpr bool fb_ibp_loop_ok() { return fb_ibp_max_hidden<S>() <= FB_IBP_LOOP_MAXW && S::NL >= 2; }
+
+template <int NW>
+struct FbIbpMasks {
+    uint32_t cand[NW], bdead[NW], sliver[NW], sdead[NW], scand[NW], dead[NW];
+    // bits [BO, BO + 64) of w |= m
+    template <int BO>
+    static __device__ __forceinline__ void put(uint32_t (&w)[NW], uint64_t m)
+    {
+        constexpr int k0 = BO >> 5, s = BO & 31;
+        const uint64_t lo = m << s;
+        w[k0] |= (uint32_t)lo;
+        if (k0 + 1 < NW) w[k0 + 1] |= (uint32_t)(lo >> 32);
+        if (s != 0 && k0 + 2 < NW) w[k0 + 2] |= (uint32_t)(m >> (64 - s));
+    }
+};
+
+template <class S, int l, int INW>
+__device__ __forceinline__ void fb_ibp_loop_layer(const SpecParams<S, double> &prm, const double (&lb)[INW], const double (&ub)[INW],
+                                                  const double (&lbd)[INW], const double (&ubd)[INW], double *scol,
+                                                  FbIbpMasks<S::NW> &mk, const uint32_t *cnt, const double *tol,
+                                                  const uint32_t *unb, const FbPruneOut &o, int64_t p, double &out_lb_rd,
+                                                  double &out_ub_ru)
+{
+    constexpr int IN = S::dim(l), OUT = S::dim(l + 1), BO = S::boff(l), N = S::N;
+    constexpr bool last = (l == S::NL - 1), first = (l == 0);
+    static_assert(IN <= INW && OUT <= 64, "layer too wide for the looped bounds kernel");
+    constexpr uint64_t full = OUT == 64 ? ~0ull : ((1ull << OUT) - 1ull);
+    uint64_t cand64 = 0, bdead64 = 0, bcand64 = 0, sliver64 = 0, sdead64 = 0;
+    // weights of neuron j: even layers are stored [out][in], odd layers [in][out] (Spec::widx)
+    constexpr int jstride = (l & 1) ? 1 : IN, istride = (l & 1) ? OUT : 1;
+    const double *wl = prm.w + S::woff(l);
+#pragma unroll 1
+    for (int j = 0; j < OUT; ++j) {
+        const double *wj = wl + j * jstride;
+        double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+            const double w = wj[i * istride];
+            const bool neg = fb_signbit(w);            // host canonicalises -0.0 to +0.0
+            const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+            mn = __dadd_rn(mn, __dmul_rn(w, a));
+            mx = __dadd_rn(mx, __dmul_rn(w, b));
+            if (first) {                               // integer inputs: both chains read the same box
+                mnd = __dadd_rd(mnd, __dmul_rd(w, a));
+                mxd = __dadd_ru(mxd, __dmul_ru(w, b));
+            } else {
+                const double ad = neg ? ubd[i] : lbd[i], bd = neg ? lbd[i] : ubd[i];
+                mnd = __dadd_rd(mnd, __dmul_rd(w, ad));
+                mxd = __dadd_ru(mxd, __dmul_ru(w, bd));
+            }
+        }
+        const double bj = prm.b[BO + j];
+        const double wlo = __dadd_rn(mn, bj), wup = __dadd_rn(mx, bj);
+        const double wld = __dadd_rd(mnd, bj), wud = __dadd_ru(mxd, bj);
+        const int idx = BO + j;
+        const uint32_t c32 = cnt ? cnt[idx] : 0u;
+        const bool c = c32 == 0, le0 = wup <= 0.0;
+        const uint64_t bit = 1ull << j;
+        if (c) cand64 |= bit;
+        if (last) { if (c) { bdead64 |= bit; bcand64 |= bit; } out_lb_rd = wld; out_ub_ru = wud; }
+        else {
+            if (c && le0) bdead64 |= bit;
+            if (c && !le0) bcand64 |= bit;
+            if (first && tol != nullptr && c && !le0 && wup <= tol[idx]) sliver64 |= bit;
+        }
+        if (o.counts16) o.counts16[p * N + idx] = (uint16_t)c32;
+        if (o.ws_lb) o.ws_lb[p * N + idx] = wlo;
+        if (o.ws_ub) o.ws_ub[p * N + idx] = wup;
+        if (o.pl_lb) o.pl_lb[p * N + idx] = wlo < 0.0 ? 0.0 : wlo;
+        if (o.pl_ub) o.pl_ub[p * N + idx] = wup < 0.0 ? 0.0 : wup;
+        if (o.lb_rd) o.lb_rd[p * N + idx] = wld;
+        if (o.ub_ru) o.ub_ru[p * N + idx] = wud;
+        if (!last) {
+            // post-activation bounds of neuron j -> this thread's column: [j][4][threads]
+            double *q = scol + j * (4 * FB_IBP_LOOP_THREADS);
+            q[0] = wlo < 0.0 ? 0.0 : wlo; q[FB_IBP_LOOP_THREADS] = wup < 0.0 ? 0.0 : wup;
+            q[2 * FB_IBP_LOOP_THREADS] = wld < 0.0 ? 0.0 : wld; q[3 * FB_IBP_LOOP_THREADS] = wud < 0.0 ? 0.0 : wud;
+        }
+    }
+    if constexpr (!last) {
+        double nlb[INW], nub[INW], nlbd[INW], nubd[INW];
+#pragma unroll
+        for (int k = 0; k < OUT; ++k) {
+            const double *q = scol + k * (4 * FB_IBP_LOOP_THREADS);
+            nlb[k] = q[0]; nub[k] = q[FB_IBP_LOOP_THREADS]; nlbd[k] = q[2 * FB_IBP_LOOP_THREADS]; nubd[k] = q[3 * FB_IBP_LOOP_THREADS];
+        }
+        if constexpr (l >= 1) {
+            // singular verification of this layer's remaining candidates (see FbIbpSink): inputs = the layer's own bounds
+            constexpr int MM = IN < OUT ? IN : OUT;
+            uint64_t todo = bcand64;
+            while (todo) {
+                const int j = __ffsll((long long)todo) - 1;
+                todo &= todo - 1;
+                const int idx = BO + j;
+                if ((__ldg(unb + (idx >> 5)) >> (idx & 31)) & 1u) continue;           // sat whatever the bounds
+                const double *wj = wl + j * jstride;
+                double q = 0.0;
+#pragma unroll
+                for (int k = 0; k < MM; ++k) {
+                    const double w = wj[k * istride];
+                    q = __dadd_rn(q, __dmul_rn(w, fb_signbit(w) ? nlb[k] : nub[k]));
+                }
+                q = __dadd_rn(q, (double)prm.b[idx]);
+                if (q <= 0.0) sdead64 |= 1ull << j;
+                if (tol != nullptr && fabs(q) <= tol[idx]) sliver64 |= 1ull << j;
+            }
+        }
+        const uint64_t scand64 = bcand64 & ~sdead64;
+        if (bdead64 == full) bdead64 &= ~1ull;               // keep-one fixes (utils/prune.py:689-691, :698-700, :703-705)
+        if (sdead64 == full) sdead64 &= ~1ull;
+        uint64_t dead64 = bdead64 | sdead64;
+        if (dead64 == full) dead64 &= ~1ull;
+        FbIbpMasks<S::NW>::template put<BO>(mk.cand, cand64); FbIbpMasks<S::NW>::template put<BO>(mk.bdead, bdead64);
+        FbIbpMasks<S::NW>::template put<BO>(mk.sliver, sliver64); FbIbpMasks<S::NW>::template put<BO>(mk.sdead, sdead64);
+        FbIbpMasks<S::NW>::template put<BO>(mk.scand, scand64); FbIbpMasks<S::NW>::template put<BO>(mk.dead, dead64);
+        fb_ibp_loop_layer<S, l + 1, INW>(prm, nlb, nub, nlbd, nubd, scol, mk, cnt, tol, unb, o, p, out_lb_rd, out_ub_ru);
+    } else {
+        // the single output neuron: candidate copied through, then cleared by the keep-one fix of its 1-element list
+        FbIbpMasks<S::NW>::template put<BO>(mk.cand, cand64);
+        FbIbpMasks<S::NW>::template put<BO>(mk.scand, bcand64);
+    }
+}
+
+template <class S>
+__global__ void __launch_bounds__(FB_IBP_LOOP_THREADS)
+fb_ibp_loop_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n, const int32_t *__restrict__ boxes,
+                   const uint32_t *__restrict__ counts, const double *__restrict__ tol,
+                   const uint32_t *__restrict__ unb, const __grid_constant__ FbPruneOut out)
+{
+    constexpr int D0 = S::D0, NW = S::NW, N = S::N;
+    constexpr int INW = fb_ibp_max_hidden<S>() > D0 ? fb_ibp_max_hidden<S>() : D0;
+    extern __shared__ __align__(16) unsigned char fb_smem[];                 // [max hidden width][4][threads] doubles
+    double *scol = reinterpret_cast<double *>(fb_smem) + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        double lb[INW], ub[INW];
+        const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
+#pragma unroll
+        for (int i = 0; i < D0; ++i) {
+            const int2 b = __ldg(bx + i);
+            lb[i] = (double)b.x; ub[i] = (double)b.y;
+        }
+        FbIbpMasks<NW> mk;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) { mk.cand[k] = 0; mk.bdead[k] = 0; mk.sliver[k] = 0; mk.sdead[k] = 0; mk.scand[k] = 0; mk.dead[k] = 0; }
+        double out_lb_rd = 0.0, out_ub_ru = 0.0;
+        fb_ibp_loop_layer<S, 0, INW>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
+                                     out_lb_rd, out_ub_ru);
+        uint32_t anysl = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (out.cand) out.cand[p * NW + k] = mk.cand[k];
+            if (out.b_dead) out.b_dead[p * NW + k] = mk.bdead[k];
+            if (out.dead) out.dead[p * NW + k] = mk.dead[k];
+            if (out.sliver) out.sliver[p * NW + k] = mk.sliver[k];
+            if (out.s_dead) out.s_dead[p * NW + k] = mk.sdead[k];
+            if (out.s_cand) out.s_cand[p * NW + k] = mk.scand[k];
+            anysl |= mk.sliver[k];
+        }
+        uint8_t v = 0;
+        if (out_lb_rd > 0.0 || out_ub_ru < 0.0) v |= FB_VERDICT_CERTIFIED;
+        if (anysl) v |= FB_VERDICT_SLIVER;
+        if (out.verdict) out.verdict[p] = v;
+        if (out.record) {
+            uint32_t *r = out.record + p * (2 * NW + 2);
+            r[0] = v;
+#pragma unroll
+            for (int k = 0; k < NW; ++k) { r[1 + k] = mk.dead[k]; r[1 + NW + k] = mk.cand[k]; }
+            r[1 + 2 * NW] = 0xffffffffu;
+        }
+    }
+}

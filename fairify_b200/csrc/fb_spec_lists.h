@@ -18,7 +18,11 @@
 #define FB_SPEC_LIST_g(X) X(20, 64, 32, 16, 8, 4, 1)
 
 // Architectures whose activation profile runs on the FP64 matrix instruction with compile-time widths (fb_specM_x.cu):
-// the four wide reference networks ...
+// the four wide reference networks, and the mid-size ones whose hidden-to-hidden layers hold most of the weights (for the
+// rest -- one hidden layer, or layers far from a multiple of 8 neurons -- the padding of the 8-column tiles and the
+// one-column logit tile cost more than the matrix instruction saves; they stay on fb_profile_spec_kernel)
 #define FB_SPEC_MMA_LIST_a(X) X(13, 100, 100, 1) X(13, 64, 64, 1)       /* AC-4, AC-5 */
 #define FB_SPEC_MMA_LIST_b(X) X(16, 150, 100, 50, 1)                    /* BM-4 */
 #define FB_SPEC_MMA_LIST_c(X) X(16, 64, 64, 1)                          /* BM-7 */
+#define FB_SPEC_MMA_LIST_d(X) X(16, 64, 16, 1) X(13, 64, 32, 16, 8, 4, 1) X(16, 64, 32, 16, 8, 4, 1) X(20, 64, 32, 16, 8, 4, 1) /* BM-1, AC-7, BM-8, GC-5 */
+// (measured and left on the FMA kernel: BM-2 16-32-16-1 70 % vs 53 % of FP64 peak with DMMA, BM-9 16-30-20-1 69 vs 49)

@@ -1,6 +1,8 @@
 // fb_spec_ops_ibp.cuh -- launcher of the specialised bounds kernel for one Spec<...>; included by the fb_specI_*.cu
 // instantiation units.
 #pragma once
+#include <cstdlib>
+
 #include "fb_launch.cuh"
 #include "fb_registry.h"
 #include "fb_spec_ibp.cuh"
@@ -24,6 +26,20 @@ struct FbSpecIbpOps {
                            const uint32_t *unb, const FbPruneOut *out, int num_sms, cudaStream_t st)
     {
         const P64 &prm = *static_cast<const P64 *>(p64);
+        // FAIRIFY_B200_IBP_UNROLLED=1 keeps the fully unrolled kernel for the shapes the looped one covers (comparisons)
+        static const bool unrolled = [] { const char *v = getenv("FAIRIFY_B200_IBP_UNROLLED"); return v && v[0] == '1'; }();
+        if constexpr (fb_ibp_loop_ok<S>()) {
+            if (!unrolled) {
+                auto k = fb_ibp_loop_kernel<S>;
+                const size_t smem = sizeof(double) * 4 * FB_IBP_LOOP_THREADS * fb_ibp_max_hidden<S>();
+                cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                const int64_t ctas = (n + FB_IBP_LOOP_THREADS - 1) / FB_IBP_LOOP_THREADS;
+                k<<<fb_grid_for(k, FB_IBP_LOOP_THREADS, smem, ctas, num_sms), FB_IBP_LOOP_THREADS, smem, st>>>(prm, n, boxes, counts,
+                                                                                                          tol, unb, *out);
+                return cudaGetLastError();
+            }
+        }
         auto k = fb_ibp_spec_kernel<S>;
         const int64_t ctas = (n + FB_IBP_THREADS - 1) / FB_IBP_THREADS;
         k<<<fb_grid_for(k, FB_IBP_THREADS, 0, ctas, num_sms), FB_IBP_THREADS, 0, st>>>(prm, n, boxes, counts, tol, unb, *out);

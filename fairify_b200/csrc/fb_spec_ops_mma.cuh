@@ -25,8 +25,18 @@ struct FbSpecMmaOps {
         return cudaGetLastError();
     }
 
-    // sample blocks per warp step: 2 when the widest layer leaves registers for it (up to 64 neurons), else 1;
+    // MS = sample blocks (of 8) per warp step.  The instantiation unit says which values it builds
+    // (FB_MMA_SPEC_MS_MASK: bit 0 = 1, bit 1 = 2, bit 2 = 4 blocks) and which one is the default;
     // FAIRIFY_B200_MMA_MS / FAIRIFY_B200_MMA_WARPS override (tuning aids)
+    template <int MS>
+    static cudaError_t go_ms(bool philox, const FbMmaNet &net, int warps, int64_t n, const int32_t *boxes, const int32_t *samples,
+                             uint64_t seed, int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *counts,
+                             int num_sms, cudaStream_t st)
+    {
+        if (philox) return go<MS, true>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
+        return go<MS, false>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
+    }
+
     static cudaError_t profile(const FbMmaNet &net, int64_t n, const int32_t *boxes, const int32_t *samples, uint64_t seed,
                                int64_t first_index, int nsamp, int chunks, int chunk_len, uint32_t *counts, int num_sms,
                                cudaStream_t st)
@@ -36,12 +46,13 @@ struct FbSpecMmaOps {
         if (const char *v = getenv("FAIRIFY_B200_MMA_WARPS")) warps = atoi(v);
         if (warps < 1 || warps > FB_MMA_WARPS) return cudaErrorInvalidValue;
         const bool philox = samples == nullptr;
-        if (ms == 2 && FB_MMA_SPEC_HAS_MS2) {
-            if (philox) return go<FB_MMA_SPEC_HAS_MS2 ? 2 : 1, true>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
-            return go<FB_MMA_SPEC_HAS_MS2 ? 2 : 1, false>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
-        }
-        if (philox) return go<1, true>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
-        return go<1, false>(net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
+#if FB_MMA_SPEC_MS_MASK & 4
+        if (ms == 4) return go_ms<4>(philox, net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
+#endif
+#if FB_MMA_SPEC_MS_MASK & 2
+        if (ms == 2) return go_ms<2>(philox, net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
+#endif
+        return go_ms<(FB_MMA_SPEC_MS_MASK & 1) ? 1 : FB_MMA_SPEC_DEFAULT_MS>(philox, net, warps, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, counts, num_sms, st);
     }
 };
 

@@ -1,7 +1,8 @@
 #!/bin/bash
-# sweep of the DMMA profile kernel's tile height / warps per CTA per model (development aid; run on the GPU box)
+# DMMA profile kernel against the FMA kernels per model, for MS = 1, 2, 4 sample blocks per warp step (development aid)
 for m in "$@"; do
-  for ms in 1 2; do for w in 4 8; do
-    FAIRIFY_B200_MMA_MS=$ms FAIRIFY_B200_MMA_WARPS=$w python tools/time_profile.py $m 20000 2>&1 | tail -1 | cut -c1-150 | sed "s/^/ms=$ms warps=$w /"
-  done; done
+  FAIRIFY_B200_MMA_PROFILE=0 python tools/time_profile.py $m 200000 2>&1 | tail -1 | cut -c1-120 | sed "s/^/fma       /"
+  for ms in 1 2 4; do
+    FAIRIFY_B200_MMA_MS=$ms python tools/time_profile.py $m 200000 2>&1 | tail -1 | cut -c1-120 | sed "s/^/dmma ms=$ms /"
+  done
 done
