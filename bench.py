@@ -11,8 +11,11 @@ its Z3 neuron queries.  A *step* is one pass over this rank's batch of partition
 Workload (config.workload): the scaled stress/AC experiment of BASELINE.json -- AC-1 weights (the AC-14
 .h5 is not in the reference; same 13-16-8-1 stack), 10^7 synthetic partitions per GPU taken from the Adult
 grid with PARTITION_THRESHOLD 4 (161.9 M boxes; rank r owns canonical indices [r*10^7, (r+1)*10^7)).
-Weak scaling: per-GPU work is fixed; with N > 1 each step ends with the NCCL all-gather of the packed
-verdict / mask records, inside the timed region.
+Weak scaling (default): per-GPU work is fixed.  `--scaling strong` reads BASELINE config 4 literally: --partitions in
+total, split into contiguous ranges over the GPUs.  With N > 1 every step's packed records -- verdict | dead mask |
+candidate mask | first counterexample sample, written by fb_ibp itself -- are all-gathered over NCCL on a second stream,
+so that the gather of step k overlaps the kernels of step k+1; the last gather is inside the timed region, and rank 0
+checks the gathered bytes of a foreign shard against its own recomputation of that shard.
 
 `value`   device-resident boxes in, device-resident masks out (kernel-only), CUDA events, max over ranks.
 `e2e`     the same batch through fb_prune_host with pinned HOST buffers: boxes copied in, masks + verdicts +
@@ -51,6 +54,16 @@ def load_ac1():
 def workload_name(n_per_gpu):
     return (f"stress/AC scaled: AC-1 weights (13-16-8-1; AC-14 .h5 absent from the reference), {n_per_gpu} synthetic "
             f"partitions per GPU = Adult grid T={GRID_T} canonical range [rank*n, (rank+1)*n), S={S_SAMPLES} Philox samples")
+
+
+def config_for(n, world, scaling):
+    """`config` of the JSON line -- the same dictionary for the GPU arm and the CPU (reference) arm."""
+    per = n if scaling == "weak" else f"{n} in total, split evenly"
+    return {"workload": workload_name(n) if scaling == "weak" else workload_name(n).replace("per GPU", "in total (strong scaling: split over the GPUs)"),
+            "model": "AC-1", "partitions_per_gpu": per, "samples": S_SAMPLES,
+            "l2": "inputs (boxes, 104 B x n) and outputs exceed the 126 MB L2; no flush needed",
+            "parallelism": f"contiguous partition range per GPU x{world}" +
+                           (", all-gather of the packed verdict / mask / counterexample records per step, overlapped with the next step" if world > 1 else "")}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -149,9 +162,9 @@ def run_reference(args):
     sample_txt = f"first {sample} partitions of the workload per step (full pre-solver, S={S_SAMPLES})"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args.partitions), "cpu_sample": sample_txt},
+        "config": config_for(args.partitions, args.gpus, args.scaling),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_txt},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "CPU arm = oracle/fairify_oracle.c (C restatement of the reference's Python/numpy path, OpenMP over "
@@ -168,7 +181,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     from fairify_b200 import engine
-    from fairify_b200.dist import pack_records
+    from fairify_b200.dist import shard_range
     from fairify_b200.domains import DOMAINS
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -190,10 +203,16 @@ def run_gpu(args):
     model = engine.Model(w, b)
     D = DOMAINS["AC"]
     grid = engine.Grid(D.columns, D.ranges, GRID_T)
-    n = args.partitions
-    first = rank * n
-    if first + n > len(grid):
-        raise SystemExit(f"grid of {len(grid)} boxes cannot give {n} per rank to {world} ranks")
+    if args.scaling == "strong":
+        n_total = args.partitions                          # BASELINE config 4 read literally: 10^7 partitions in all
+        first, n = shard_range(n_total, rank, world)
+    else:
+        n = args.partitions
+        first = rank * n
+        n_total = world * n
+    if n_total > len(grid):
+        raise SystemExit(f"grid of {len(grid)} boxes cannot give {n_total} partitions")
+    nmax = shard_range(n_total, 0, world)[1] if args.scaling == "strong" else n
     lo = [D.ranges[c][0] for c in D.columns]; hi = [D.ranges[c][1] for c in D.columns]
     tol = torch.as_tensor(model.tolerance(lo, hi)).cuda()
 
@@ -203,11 +222,21 @@ def run_gpu(args):
     g0.record(); boxes = grid.boxes(first, n); g1.record(); torch.cuda.synchronize()
     boxgen_ms = g0.elapsed_time(g1)
     counts32 = torch.empty((n, model.N), dtype=torch.int32, device="cuda")
-    outs, po = model._alloc_outputs(n, engine.DEFAULT_OUTPUTS)
+    # per-partition record [verdict | dead mask | candidate mask | first counterexample sample], written by fb_ibp itself;
+    # two copies so that the all-gather of step k (on its own stream) overlaps the kernels of step k+1
     NW = model.NW
-    rec_w = 1 + 2 * NW
-    packed = torch.empty((n, rec_w), dtype=torch.int32, device="cuda")
-    gathered = torch.empty((world * n, rec_w), dtype=torch.int32, device="cuda") if world > 1 else None
+    rec_w = 2 * NW + 2
+    outs, po = model._alloc_outputs(n, engine.DEFAULT_OUTPUTS + ("record",))
+    packed = [outs["record"], torch.empty_like(outs["record"])]
+    pos = [po, type(po)()]
+    for k_ in engine.ALL_OUTPUTS:
+        setattr(pos[1], k_, getattr(po, k_))
+    pos[1].record = packed[1].data_ptr()
+    # (shards may differ by one partition under strong scaling: the collective works on nmax rows per rank)
+    send = [torch.zeros((nmax, rec_w), dtype=torch.int32, device="cuda") for _ in range(2)] if (world > 1 and nmax != n) else None
+    gathered = [torch.empty((world * nmax, rec_w), dtype=torch.int32, device="cuda") for _ in range(2)] if world > 1 else None
+    comm = torch.cuda.Stream() if world > 1 else None
+    gather_done = [None, None]
 
     import ctypes as C
     from fairify_b200 import _lib
@@ -215,21 +244,40 @@ def run_gpu(args):
     stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
     ptr = lambda t: C.c_void_p(t.data_ptr())
 
+    step_no = [0]
+
     def step(timers=None):
+        k = step_no[0] & 1
+        step_no[0] += 1
         if timers:
             timers[0].record()
         _lib.check(L.fb_profile(model._h, n, ptr(boxes), None, S_SAMPLES, C.c_uint64(SEED), first, ptr(counts32), stream()))
         if timers:
             timers[1].record()
-        _lib.check(L.fb_ibp(model._h, n, ptr(boxes), ptr(counts32), ptr(tol), C.byref(po), stream()))
+        if world > 1 and gather_done[k] is not None:
+            torch.cuda.current_stream().wait_event(gather_done[k])      # the gather of two steps ago still reads packed[k]
+        _lib.check(L.fb_ibp(model._h, n, ptr(boxes), ptr(counts32), ptr(tol), C.byref(pos[k]), stream()))
         if timers:
             timers[2].record()
         if world > 1:
-            pack_records(outs["verdict"], outs["dead"], outs["cand"], out=packed)
-            dist.all_gather_into_tensor(gathered, packed)
+            ready = torch.cuda.Event()
+            ready.record()
+            comm.wait_event(ready)
+            with torch.cuda.stream(comm):
+                src = packed[k]
+                if send is not None:
+                    send[k][:n].copy_(packed[k]); src = send[k]
+                dist.all_gather_into_tensor(gathered[k], src)
+                gather_done[k] = torch.cuda.Event()
+                gather_done[k].record()
+
+    def drain():
+        if world > 1:
+            torch.cuda.current_stream().wait_stream(comm)
 
     for _ in range(args.warmup):
         step()
+    drain()
     peak_tf, _ = engine.fp64_peak(4096)
     peak_tf = max(peak_tf, engine.fp64_peak(4096)[0])
 
@@ -242,6 +290,7 @@ def run_gpu(args):
     t0.record()
     for k in range(args.steps):
         step(timers[k])
+    drain()
     t1.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -252,7 +301,7 @@ def run_gpu(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(prof_ms, op=dist.ReduceOp.MAX)
     total_ms = float(ms.item())
-    value = world * n * args.steps / (total_ms * 1e-3)
+    value = n_total * args.steps / (total_ms * 1e-3)
 
     # end to end: host boxes in, host masks / verdicts / counts out, every step
     hboxes = boxes.cpu().pin_memory()
@@ -269,7 +318,7 @@ def run_gpu(args):
     ems = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ems, op=dist.ReduceOp.MAX)
-    e2e_value = world * n * args.steps / (float(ems.item()) * 1e-3)
+    e2e_value = n_total * args.steps / (float(ems.item()) * 1e-3)
     h2d = hboxes.numel() * 4 + htol.numel() * 8
     d2h = sum(t.numel() * t.element_size() for t in hout.values())
     # the device path and the host path must agree byte for byte
@@ -290,17 +339,123 @@ def run_gpu(args):
     s1.record(); torch.cuda.synchronize()
     screen_ms = s0.elapsed_time(s1)
 
+    # N > 1: what the all-gather delivered for a foreign shard must be what this rank computes for that shard itself
+    gather_checked = None
+    if world > 1 and rank == 0:
+        last = (step_no[0] - 1) & 1
+        f1, c1 = (shard_range(n_total, 1, world) if args.scaling == "strong" else (n, n))
+        chk = min(c1, 200_000)
+        bx1 = grid.boxes(f1, chk)
+        r1 = model.prune(bx1, S=S_SAMPLES, seed=SEED, first_index=f1, tol=tol, want=("record",))
+        gather_checked = bool(torch.equal(gathered[last][nmax: nmax + chk], r1.t["record"])) and \
+            bool(torch.equal(gathered[last][:min(n, chk)], packed[last][:min(n, chk)]))
+        if not gather_checked:
+            raise SystemExit("bench.py: the gathered records differ from a recomputation of the foreign shard")
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
+
+    def timed(fn, reps=2):
+        for _ in range(reps):
+            a_, b_ = ev(), ev()
+            a_.record(); fn(); b_.record(); torch.cuda.synchronize()
+        return a_.elapsed_time(b_)
+
+    z = np.load(os.path.join(ROOT, "tests", "golden", "weights.npz"))
+
+    def load(name):
+        Lk = int(z[f"{name}/L"])
+        return engine.Model([z[f"{name}/w{l}"] for l in range(Lk)], [z[f"{name}/b{l}"] for l in range(Lk)])
+
+    # BASELINE configs 1 and 2: the src/GC grid x GC-1 (201 partitions) and the src/AC grid x AC-1 (16 000): the full
+    # pre-solver + sampled counterexample screen in one batch, and the same through the drop-in `utils` API the
+    # unchanged drivers call (sound_prune* + prune_neurons + 3 x get_y_pred per partition, src/AC/Verify-AC.py:117-274),
+    # whose window batching answers each call from one launch per 4096 partitions
+    src_grids = {}
+    try:
+        import contextlib, io
+        import pandas as pd
+        import importlib
+        from utils.input_partition import partition, partitioned_ranges
+        import utils.prune as UP
+        from utils.verif_utils import get_y_pred
+        for tag, name, fn in (("src/GC x GC-1", "GC-1", UP.sound_prune_german), ("src/AC x AC-1", "AC-1", UP.sound_prune)):
+            Dm = DOMAINS[name.split("-")[0]]
+            mk = load(name)
+            gk = engine.Grid(Dm.columns, Dm.ranges, Dm.threshold)
+            bk = gk.boxes()
+            tk = torch.as_tensor(mk.tolerance([Dm.ranges[c][0] for c in Dm.columns], [Dm.ranges[c][1] for c in Dm.columns])).cuda()
+            pak = Dm.columns.index(Dm.pa[0])
+            ms_batch = timed(lambda: (mk.prune(bk, S=S_SAMPLES, seed=SEED, tol=tk, want=engine.DEFAULT_OUTPUTS + ("record",)),
+                                      mk.partition_screen(bk, pak, S=S_SAMPLES, seed=SEED)))
+            wk = [z[f"{name}/w{l}"] for l in range(mk.L)]; bkk = [z[f"{name}/b{l}"] for l in range(mk.L)]
+            mod = importlib.import_module(f"utils.{name}-Model-Functions")
+            df = pd.DataFrame(np.zeros((2, Dm.d + 1)), columns=Dm.columns + [Dm.label])
+            rd = Dm.copy_ranges()
+            t0 = time.perf_counter()
+            p_list = partitioned_ranges(rd.keys(), Dm.pa, partition(rd, Dm.threshold), rd)
+            t_grid = time.perf_counter() - t0
+            count = min(len(p_list), 2000)
+            np.random.seed(1)
+            with contextlib.redirect_stdout(io.StringIO()):
+                t0 = time.perf_counter()
+                for pp in p_list[:count]:
+                    out = fn(df, wk, bkk, S_SAMPLES, mod.layer_net, pp)
+                    pr_w, pr_b = UP.prune_neurons(wk, bkk, out[5])
+                    sim = out[7].to_numpy()
+                    get_y_pred(mod.net, wk, bkk, sim); get_y_pred(mod.net, pr_w, pr_b, sim); get_y_pred(mod.net, wk, bkk, sim[:200])
+                t_drop = time.perf_counter() - t0
+            src_grids[tag] = {"partitions": len(gk), "batch_prune_plus_screen_ms": ms_batch,
+                              "batch_evals_per_s": len(gk) / (ms_batch * 1e-3),
+                              "dropin_partitions_timed": count, "dropin_ms_per_partition": 1e3 * t_drop / count,
+                              "dropin_partitioned_ranges_s": t_grid,
+                              "reference_s_per_partition": "0.17-2.9 (BASELINE.md section 2, same calls in the Python reference)"}
+    except Exception as exc:
+        src_grids = {"error": repr(exc)}
+
+    # BASELINE config 5: the relaxed / targeted / targeted2 Adult grids (3 290 112 / 205 632 / 1 096 704 partitions,
+    # PARTITION_THRESHOLD 6) on every Adult model whose .h5 exists (AC-1..12): full pre-solver with the packed record,
+    # and on a window of the relaxed grid the relaxed counterexample screen (PA race, RA age +-5)
+    ac_sweep = {}
+    try:
+        DA = DOMAINS["AC"]
+        grids5 = {"relaxed": {}, "targeted": {"age": [30, 35]}, "targeted2": {"education": [9, 10]}}
+        gs = {}
+        for gname, override in grids5.items():
+            rd = DA.copy_ranges()
+            rd.update(override)
+            gs[gname] = engine.Grid(DA.columns, rd, 6)
+        tolA = None
+        for k in range(1, 13):
+            name = f"AC-{k}"
+            mk = load(name)
+            tk = torch.as_tensor(mk.tolerance([DA.ranges[c][0] for c in DA.columns], [DA.ranges[c][1] for c in DA.columns])).cuda()
+            row = {"weights": mk.P}
+            for gname, gk in gs.items():
+                nk = len(gk) if mk.P < 4000 else min(len(gk), 400_000)       # (the four wide models: a window, extrapolate)
+                bk = gk.boxes(0, nk)
+                ms_k = timed(lambda: mk.prune(bk, S=S_SAMPLES, seed=SEED, tol=tk, want=("record",)), reps=1 if nk > 1_000_000 else 2)
+                rate = nk / (ms_k * 1e-3)
+                row[gname] = {"partitions": len(gk), "timed": nk, "evals_per_s": rate,
+                              "fp64_frac": rate * S_SAMPLES * (2.0 * mk.P + mk.N) / 1e12 / peak_tf}
+                del bk
+            wk_ = min(len(gs["relaxed"]), 200_000)
+            bk = gs["relaxed"].boxes(0, wk_)
+            ms_r = timed(lambda: mk.partition_screen(bk, DA.columns.index("race"), S=S_SAMPLES, seed=SEED,
+                                                     ra_col=DA.columns.index("age"), ra_threshold=5))
+            row["relaxed_screen_partitions_per_s"] = wk_ / (ms_r * 1e-3)
+            ac_sweep[name] = row
+            del bk, mk
+    except Exception as exc:
+        ac_sweep = {"error": repr(exc)}
 
     # side numbers for BASELINE.json's BM-1..8 sweep (full pre-solver + sampled counterexample screen per model on a
     # window of the stress/BM grid); not part of the headline
     bm_sweep = {}
     try:
         from fairify_b200.domains import STRESS_THRESHOLD
-        z = np.load(os.path.join(ROOT, "tests", "golden", "weights.npz"))
         DB = DOMAINS["BM"]
         gb = engine.Grid(DB.columns, DB.ranges, STRESS_THRESHOLD["BM"])
         nb = min(20000, len(gb))
@@ -309,15 +464,16 @@ def run_gpu(args):
         bpa = DB.columns.index(DB.pa[0])
         for k in range(1, 9):
             name = f"BM-{k}"
-            Lk = int(z[f"{name}/L"])
-            mk = engine.Model([z[f"{name}/w{l}"] for l in range(Lk)], [z[f"{name}/b{l}"] for l in range(Lk)])
+            mk = load(name)
             tk = torch.as_tensor(mk.tolerance(blo, bhi)).cuda()
             for it in range(2):                                   # first pass warms the kernels up
                 b0, b1, b2 = ev(), ev(), ev()
                 b0.record(); mk.prune(bboxes, S=S_SAMPLES, seed=SEED, tol=tk); b1.record()
                 mk.partition_screen(bboxes, bpa, S=S_SAMPLES, seed=SEED); b2.record(); torch.cuda.synchronize()
+            rate_k = nb / (b0.elapsed_time(b1) * 1e-3)
             bm_sweep[name] = {"weights": mk.P, "kernels": "specialised" if mk.specialised else "runtime-shape",
-                              "prune_evals_per_s": nb / (b0.elapsed_time(b1) * 1e-3),
+                              "prune_evals_per_s": rate_k,
+                              "fp64_frac": rate_k * S_SAMPLES * (2.0 * mk.P + mk.N) / 1e12 / peak_tf,
                               "screen_partitions_per_s": nb / (b1.elapsed_time(b2) * 1e-3)}
     except Exception as exc:                                      # a side measurement must never cost the headline line
         bm_sweep = {"error": repr(exc)}
@@ -345,11 +501,9 @@ def run_gpu(args):
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(n), "model": "AC-1", "partitions_per_gpu": n, "samples": S_SAMPLES,
-                   "l2": "inputs (boxes, 104 B x n) and outputs exceed the 126 MB L2; no flush needed",
-                   "parallelism": f"contiguous partition range per GPU x{world}" + (", all-gather of verdict+mask records per step" if world > 1 else "")},
+        "config": config_for(args.partitions, world, args.scaling),
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "host_equals_device": same},
@@ -371,6 +525,9 @@ def run_gpu(args):
                   "box_generation_boxes_per_s": n / (boxgen_ms * 1e-3),
                   "partition_screen_pairs_per_s": ns * S_SAMPLES / (screen_ms * 1e-3),
                   "fp64_peak_tflops_measured": peak_tf,
+                  "gathered_records_equal_recomputation": gather_checked,
+                  "src_grids_configs_1_2": src_grids,
+                  "relaxed_targeted_ac_models_config_5": ac_sweep,
                   "bm_sweep_20000_partitions_S1000": bm_sweep},
     }
     print(json.dumps(line), flush=True)
@@ -385,7 +542,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--partitions", type=int, default=10_000_000, help="partitions per GPU")
+    ap.add_argument("--partitions", type=int, default=10_000_000, help="partitions per GPU (weak) or in total (strong)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --partitions per GPU (default, the headline); strong: --partitions in total, split over the GPUs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

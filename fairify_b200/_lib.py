@@ -17,6 +17,7 @@ EXPORTS = [
     "fb_release_cache",
     "fb_grid_create", "fb_grid_destroy", "fb_grid_size", "fb_grid_boxes", "fb_grid_locate", "fb_profile", "fb_ibp", "fb_prune",
     "fb_prune_host", "fb_prune_noalloc", "fb_forward_f64", "fb_forward_f32", "fb_pair_screen", "fb_partition_screen", "fb_heuristic", "fb_fp64_peak",
+    "fb_partition_screen_ex", "fb_hybrid_predict", "fb_profile_nearzero",
 ]
 
 
@@ -66,6 +67,9 @@ def lib():
     L.fb_forward_f32.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_pair_screen.argtypes = [vp, i64, vp, i32, vp, i32, vp, vp, vp, vp]
     L.fb_partition_screen.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, vp, vp, vp, vp, vp]
+    L.fb_partition_screen_ex.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.fb_hybrid_predict.argtypes = [vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp]
+    L.fb_profile_nearzero.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, vp, vp]
     L.fb_heuristic.argtypes = [vp, i64, vp, vp, vp, vp, vp, C.c_double, vp, vp, vp]
     L.fb_fp64_peak.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     _lib = L

@@ -881,30 +881,56 @@ extern "C" int fb_pair_screen(const fb_model *m, int64_t rows, const float *X, i
 }
 
 __global__ void __launch_bounds__(256)
-fb_ce_unpack_kernel(int64_t n, int d, int pa_col, const int32_t *__restrict__ boxes,
+fb_ce_unpack_kernel(int64_t n, int d, int pa_col, bool relaxed, const int32_t *__restrict__ boxes,
                     const unsigned long long *__restrict__ key, int32_t *__restrict__ ce_sample,
-                    int32_t *__restrict__ pa_pos, int32_t *__restrict__ pa_neg, uint8_t *__restrict__ verdict)
+                    int32_t *__restrict__ pa_pos, int32_t *__restrict__ pa_neg, int32_t *__restrict__ ra_dpos,
+                    int32_t *__restrict__ ra_dneg, uint8_t *__restrict__ verdict, uint32_t *__restrict__ record, int rec_words)
 {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
         const unsigned long long k = key[p];
-        if (k == ~0ull) { ce_sample[p] = -1; pa_pos[p] = -1; pa_neg[p] = -1; continue; }
-        const int lo = boxes[p * (2 * d) + 2 * pa_col];
-        ce_sample[p] = (int32_t)(k >> 32);
-        pa_pos[p] = lo + (int32_t)((k >> 16) & 0xffffu);
-        pa_neg[p] = lo + (int32_t)(k & 0xffffu);
-        if (verdict) verdict[p] |= FB_VERDICT_CE;
+        int32_t cs = -1, vp = -1, vn = -1, dp = 0, dn = 0;
+        uint8_t flag = 0;
+        if (k == FB_SCREEN_SKIPPED) flag = FB_VERDICT_SKIPPED;
+        else if (k != ~0ull) {
+            const int lo = boxes[p * (2 * d) + 2 * pa_col];
+            cs = (int32_t)(k >> 32);
+            if (relaxed) {
+                vp = lo + (int32_t)((k >> 24) & 0xffu); vn = lo + (int32_t)((k >> 16) & 0xffu);
+                dp = (int32_t)((k >> 8) & 0xffu) - 128; dn = (int32_t)(k & 0xffu) - 128;
+            } else {
+                vp = lo + (int32_t)((k >> 16) & 0xffffu); vn = lo + (int32_t)(k & 0xffffu);
+            }
+            flag = FB_VERDICT_CE;
+        }
+        if (ce_sample) ce_sample[p] = cs;
+        if (pa_pos) pa_pos[p] = vp;
+        if (pa_neg) pa_neg[p] = vn;
+        if (ra_dpos) ra_dpos[p] = dp;
+        if (ra_dneg) ra_dneg[p] = dn;
+        if (verdict && flag) verdict[p] |= flag;
+        if (record) {
+            uint32_t *r = record + p * rec_words;
+            r[rec_words - 1] = (uint32_t)cs;
+            if (flag) r[0] |= flag;
+        }
     }
 }
 
-extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
-                                   uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
-                                   int32_t *pa_neg, uint8_t *verdict, void *stream)
+extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                      uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_threshold,
+                                      int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg,
+                                      uint8_t *verdict, uint32_t *record, void *stream)
 {
     if (int rc = fb_check_batch("fb_partition_screen", m, n, boxes, S, true)) return rc;
-    if (pa_col < 0 || pa_col >= m->gen.dims[0]) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: protected column %d out of range", pa_col);
+    const int d = m->gen.dims[0];
+    if (pa_col < 0 || pa_col >= d) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: protected column %d out of range", pa_col);
+    if (ra_col >= d || ra_col == pa_col) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: relaxed column %d out of range (or equal to the protected column)", ra_col);
+    if (ra_col < 0) { ra_col = -1; ra_threshold = 0; }
+    if (ra_threshold < 0 || ra_threshold > FB_SCREEN_MAX_THR)
+        return fb_fail(FB_ERR_UNSUPPORTED, "fb_partition_screen: relaxed threshold %d (supported: 0..%d)", ra_threshold, FB_SCREEN_MAX_THR);
     if (n == 0) return FB_OK;
-    if (!ce_sample || !pa_pos || !pa_neg) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: null output");
+    if (!ce_sample && !record && !verdict) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: no output requested");
     cudaStream_t st = (cudaStream_t)stream;
     int chunks, chunk_len;
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
@@ -913,25 +939,156 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
     FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
     if (fb_use_spec(m)) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
-                                          chunk_len, pa_col, (unsigned long long *)key.p, m->num_sms, st));
-    } else if (fb_use_tiled_profile(m)) {
+                                          chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));
+    } else if (fb_use_tiled_profile(m) && ra_col < 0) {
+        // (the tiled float32 screen of the big runtime-shape networks sweeps the protected column only)
         if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, (unsigned long long *)key.p, st)) return rc;
     } else {
         const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
         if (samples == nullptr) {
             auto k = fb_partition_screen_gen_kernel<true>;
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, m->num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, (unsigned long long *)key.p);
+                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, ra_col, ra_threshold,
+                (unsigned long long *)key.p);
         } else {
             auto k = fb_partition_screen_gen_kernel<false>;
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, m->num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, (unsigned long long *)key.p);
+                m->gen, n, boxes, samples, seed, first_index, S, chunks, chunk_len, pa_col, ra_col, ra_threshold,
+                (unsigned long long *)key.p);
         }
         FB_CUDA(cudaGetLastError());
     }
     const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)m->num_sms * 8);
-    fb_ce_unpack_kernel<<<grid, 256, 0, st>>>(n, m->gen.dims[0], pa_col, boxes, (const unsigned long long *)key.p,
-                                              ce_sample, pa_pos, pa_neg, verdict);
+    fb_ce_unpack_kernel<<<grid, 256, 0, st>>>(n, d, pa_col, ra_col >= 0, boxes, (const unsigned long long *)key.p, ce_sample,
+                                              pa_pos, pa_neg, ra_dpos, ra_dneg, verdict, record, 2 * ((m->gen.N + 31) / 32) + 2);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                   uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
+                                   int32_t *pa_neg, uint8_t *verdict, void *stream)
+{
+    if (n > 0 && (!ce_sample || !pa_pos || !pa_neg)) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: null output");
+    return fb_partition_screen_ex(m, n, boxes, samples, S, seed, first_index, pa_col, -1, 0, ce_sample, pa_pos, pa_neg, nullptr,
+                                  nullptr, verdict, nullptr, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// hybrid prediction: find_partition_result_for_point + hybrid_predict, src/AC/Verify-AC-experiment-new2.py:587-638.
+// Per row: the partition that contains it (index arithmetic), that partition's recorded verdict, and the logit of the
+// model the verdict selects -- the "fairer" model where the partition was found unfair ('sat'), the original one
+// everywhere else ('unsat', 'unknown', not evaluated, outside every partition).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+fb_hybrid_select_kernel(int64_t rows, const int64_t *__restrict__ index, const uint8_t *__restrict__ status,
+                        const float *__restrict__ y_orig, const float *__restrict__ y_fair, float *__restrict__ logit,
+                        uint8_t *__restrict__ route, unsigned int *__restrict__ counters)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += stride) {
+        const int64_t idx = index[r];
+        const uint8_t st = idx < 0 ? (uint8_t)FB_STATUS_NONE : status[idx];
+        const uint8_t rt = st <= FB_STATUS_UNKNOWN ? st : (uint8_t)FB_STATUS_NONE;
+        logit[r] = (rt == FB_STATUS_SAT) ? y_fair[r] : y_orig[r];
+        if (route) route[r] = rt;
+        if (counters) atomicAdd(&counters[rt], 1u);
+    }
+}
+
+extern "C" int fb_hybrid_predict(const fb_grid *g, const fb_model *original, const fb_model *fairer, int64_t rows,
+                                 const double *X64, const float *X32, const uint8_t *status, float *logit, uint8_t *route,
+                                 uint32_t *counters, void *stream)
+{
+    if (!g || !original || !fairer || rows < 0) return fb_fail(FB_ERR_INVALID, "fb_hybrid_predict: bad argument");
+    if (original->gen.dims[0] != g->g.d || fairer->gen.dims[0] != g->g.d)
+        return fb_fail(FB_ERR_INVALID, "fb_hybrid_predict: the models take %d / %d features, the grid has %d", original->gen.dims[0],
+                       fairer->gen.dims[0], g->g.d);
+    if (rows == 0) return FB_OK;
+    if (!X64 || !X32 || !status || !logit) return fb_fail(FB_ERR_INVALID, "fb_hybrid_predict: null argument");
+    if (int rc = fb_check_device("fb_hybrid_predict", original)) return rc;
+    if (int rc = fb_check_device("fb_hybrid_predict", fairer)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    DevBuf idx(original->device, st), yo(original->device, st), yf(original->device, st);
+    FB_CUDA(idx.alloc(sizeof(int64_t) * rows));
+    FB_CUDA(yo.alloc(sizeof(float) * rows));
+    FB_CUDA(yf.alloc(sizeof(float) * rows));
+    if (int rc = fb_grid_locate(g, rows, X64, (int64_t *)idx.p, nullptr, stream)) return rc;
+    if (int rc = fb_forward_f32(original, rows, X32, nullptr, (float *)yo.p, stream)) return rc;
+    if (int rc = fb_forward_f32(fairer, rows, X32, nullptr, (float *)yf.p, stream)) return rc;
+    const int grid = (int)std::min<int64_t>((rows + 255) / 256, (int64_t)original->num_sms * 8);
+    fb_hybrid_select_kernel<<<grid, 256, 0, st>>>(rows, (const int64_t *)idx.p, status, (const float *)yo.p, (const float *)yf.p,
+                                                  logit, route, counters);
+    FB_CUDA(cudaGetLastError());
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// How close do the sampled pre-activations come to zero, relative to the size of their terms?  The activation counts
+// depend only on signs; the reference obtains its pre-activations from numpy's BLAS dgemv, whose summation order is not
+// specified, while every kernel here sums in ascending input order.  The two can disagree on a sign only if
+// |pre-activation| is within a few rounding errors of sum_i |w_i x_i|.  This diagnostic pass (one sample per thread,
+// weights from global memory: not a fast path) counts the (sample, neuron) pairs with
+//     |pre| <= 2^-40 * (sum_i |w_i x_i| + |b|)
+// and reports the smallest ratio seen, so that "no sign depends on the summation order" is a measured statement.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+fb_nearzero_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples,
+                   uint64_t seed, int64_t first_index, int nsamp, unsigned long long *__restrict__ count,
+                   unsigned long long *__restrict__ min_ratio_bits)
+{
+    const int D0 = net.dims[0];
+    double a[FB_MAXW], y[FB_MAXW];
+    unsigned long long mine = 0;
+    double best = 1.0;
+    const int64_t total = n * (int64_t)nsamp;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u < total; u += stride) {
+        const int64_t p = u / nsamp;
+        const int s = (int)(u - p * nsamp);
+        const int32_t *box = boxes + p * (2 * D0);
+        if (samples == nullptr) fb_draw_row<double>(box, D0, fb_draw_group(fb_box_widest(box, D0)), (uint32_t)s, first_index + p, seed, a);
+        else for (int i = 0; i < D0; ++i) a[i] = (double)__ldg(samples + ((int64_t)p * nsamp + s) * D0 + i);
+        double *in = a, *out = y;
+        for (int l = 0; l < net.L; ++l) {
+            const int IN = net.dims[l], OUT = net.dims[l + 1];
+            const double *w = net.W64 + net.woff[l], *b = net.B64 + net.boff[l];
+            for (int j = 0; j < OUT; ++j) {
+                double acc = 0.0, mag = 0.0;
+                for (int i = 0; i < IN; ++i) {
+                    const double wt = __ldg(w + (int64_t)i * OUT + j);
+                    acc = __fma_rn(wt, in[i], acc);
+                    mag = __fma_rn(fabs(wt), fabs(in[i]), mag);
+                }
+                const double pre = __dadd_rn(acc, __ldg(b + j));
+                mag = __dadd_rn(mag, fabs(__ldg(b + j)));
+                if (mag > 0.0) {
+                    const double ratio = fabs(pre) / mag;
+                    if (ratio <= 0x1p-40) ++mine;
+                    best = fmin(best, ratio);
+                }
+                out[j] = (l == net.L - 1) ? pre : (pre > 0.0 ? pre : 0.0);
+            }
+            double *t = in; in = out; out = t;
+        }
+    }
+    if (mine) atomicAdd(count, mine);
+    atomicMin(min_ratio_bits, (unsigned long long)__double_as_longlong(best));       // non-negative doubles order like integers
+}
+
+extern "C" int fb_profile_nearzero(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                                   uint64_t seed, int64_t first_index, uint64_t *count, double *min_ratio, void *stream)
+{
+    if (int rc = fb_check_batch("fb_profile_nearzero", m, n, boxes, S, true)) return rc;
+    if (!count || !min_ratio) return fb_fail(FB_ERR_INVALID, "fb_profile_nearzero: null output");
+    cudaStream_t st = (cudaStream_t)stream;
+    const double one = 1.0;
+    FB_CUDA(cudaMemsetAsync(count, 0, sizeof(uint64_t), st));
+    FB_CUDA(cudaMemcpyAsync(min_ratio, &one, sizeof(double), cudaMemcpyHostToDevice, st));
+    if (n == 0) return FB_OK;
+    const int grid = (int)std::min<int64_t>((n * S + 127) / 128, (int64_t)m->num_sms * 16);
+    fb_nearzero_kernel<<<grid, 128, 0, st>>>(m->gen, n, boxes, samples, seed, first_index, S, (unsigned long long *)count,
+                                             (unsigned long long *)min_ratio);
     FB_CUDA(cudaGetLastError());
     return FB_OK;
 }

@@ -217,3 +217,9 @@ __device__ __forceinline__ VecD<K> fb_add(const VecD<K> &a, double b)
 #define FB_VERDICT_CERTIFIED 1u     // output logit provably one-signed over the box (outward-rounded enclosure)
 #define FB_VERDICT_CE        2u     // sampled counterexample pair found by the partition screen
 #define FB_VERDICT_SLIVER    4u     // some neuron's bound is within rounding error of 0: host Z3 decides s_dead
+#define FB_VERDICT_SKIPPED   8u     // the partition screen could not encode this box (protected range too wide)
+// partition status codes of the hybrid prediction
+#define FB_STATUS_NONE 0
+#define FB_STATUS_SAT 1
+#define FB_STATUS_UNSAT 2
+#define FB_STATUS_UNKNOWN 3

@@ -431,7 +431,12 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
     for (int64_t p = blockIdx.x; p < n; p += gridDim.x) {
         const int32_t *box = boxes + p * (2 * D0);
         const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
-        const int W = pa_hi - pa_lo + 1;
+        const uint32_t Wu = (uint32_t)(pa_hi - pa_lo + 1);
+        if (Wu == 0 || Wu > FB_SCREEN_MAX_W_STRICT) {                      // does not fit the key's 16-bit fields
+            if (tid == 0) ce_key[p] = FB_SCREEN_SKIPPED;
+            continue;
+        }
+        const int W = (int)Wu;
         const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
         const int64_t pidx = first_index + p;
         if (tid == 0) *s_best = ~0ull;
@@ -774,13 +779,15 @@ template <bool PHILOX>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS)
 fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes,
                                const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp,
-                               int chunks, int chunk_len, int pa_col, unsigned long long *__restrict__ ce_key)
+                               int chunks, int chunk_len, int pa_col, int ra_col, int ra_thr,
+                               unsigned long long *__restrict__ ce_key)
 {
     const int D0 = net.dims[0];
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t units = n * chunks;
+    const bool relaxed = ra_col >= 0;
     float x0[FB_MAXW], a[FB_MAXW], y[FB_MAXW];
     for (int64_t u = gwarp; u < units; u += nwarps) {
         const int64_t p = u / chunks;
@@ -788,7 +795,12 @@ fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__res
         const int s0 = c * chunk_len;
         const int s1 = min(nsamp, s0 + chunk_len);
         const int32_t *box = boxes + p * (2 * D0);
-        const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
+        const int pa_lo = __ldg(box + 2 * pa_col);
+        const uint32_t W = (uint32_t)(__ldg(box + 2 * pa_col + 1) - pa_lo + 1);
+        if (W == 0 || W > (relaxed ? FB_SCREEN_MAX_W_RELAXED : FB_SCREEN_MAX_W_STRICT)) {
+            if (lane == 0 && c == 0) ce_key[p] = FB_SCREEN_SKIPPED;
+            continue;
+        }
         const int64_t pidx = first_index + p;
         const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
         unsigned long long best = ~0ull;
@@ -801,20 +813,17 @@ fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__res
                 const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
                 for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);
             }
-            bool havep = false, haven = false;
-            int vp = 0, vn = 0;
-            FbGenReluVisit<float> vis;
-            for (int v = pa_lo; v <= pa_hi; ++v) {
+            const int ra_val = relaxed ? (int)x0[ra_col] : 0;
+            auto ev = [&](int v, int r) {
                 for (int i = 0; i < D0; ++i) a[i] = x0[i];
                 a[pa_col] = (float)v;
-                const float yv = fb_gen_forward<float>(net, net.W32, net.B32, a, y, vis);
-                if (yv > 0.0f && !havep) { havep = true; vp = v; }
-                if (yv < 0.0f && !haven) { haven = true; vn = v; }
-            }
-            const bool ce = active && havep && haven;
-            if (ce && best == ~0ull)
-                best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)(vp - pa_lo) << 16) |
-                       (unsigned long long)(uint32_t)(vn - pa_lo);
+                if (relaxed) a[ra_col] = (float)r;
+                FbGenReluVisit<float> vis;
+                return fb_gen_forward<float>(net, net.W32, net.B32, a, y, vis);
+            };
+            const uint32_t low = fb_screen_sample(ev, pa_lo, W, relaxed, ra_val, ra_thr);
+            const bool ce = active && low != 0xffffffffu;
+            if (ce && best == ~0ull) best = ((unsigned long long)(uint32_t)s << 32) | low;
             if (__any_sync(0xffffffffu, ce)) break;
         }
         const uint32_t hi = (uint32_t)(best >> 32);

@@ -30,7 +30,8 @@ struct FbSpecFwdEntry {
                                const float *alts, uint8_t *orig_pred, int32_t *first_flip, int num_sms, cudaStream_t st);
     cudaError_t (*partition_screen)(const void *p32, bool philox, int64_t n, const int32_t *boxes,
                                     const int32_t *samples, uint64_t seed, int64_t first_index, int nsamp, int chunks,
-                                    int chunk_len, int pa_col, unsigned long long *ce_key, int num_sms, cudaStream_t st);
+                                    int chunk_len, int pa_col, int ra_col, int ra_thr, unsigned long long *ce_key, int num_sms,
+                                    cudaStream_t st);
 };
 
 struct FbSpecProfileEntry {

@@ -207,14 +207,61 @@ fb_pair_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int
 // ---------------------------------------------------------------------------------------------------
 // per-partition sampled counterexample screen (the property the drivers hand to Z3,
 // src/AC/Verify-AC.py:137-156): one warp per (partition, chunk), lanes are samples; the protected
-// column is swept over the partition's own range.  Result: packed 64-bit key
-// (sample << 32 | (v_pos - lo) << 16 | (v_neg - lo)), atomicMin'ed into ce_key[p] (pre-set to ~0).
+// column is swept over the partition's own range.  Result: packed 64-bit key (sample << 32 | fields of
+// fb_screen_sample), atomicMin'ed into ce_key[p] (pre-set to ~0).
+//
+// Relaxed queries (relaxed/AC/Verify-AC.py:48-51, :128-132 with in_const_diff_adult, utils/verif_utils.py:859-867):
+// the two points may also differ in one more attribute RA by at most `thr`.  Only the first point has to lie in the
+// partition (in_const_domain_* bounds x' on the protected columns alone, :846-854), so the second point's RA value
+// ranges over a - thr .. a + thr around the sample's own value a, unclipped.
 // ---------------------------------------------------------------------------------------------------
+#define FB_SCREEN_SKIPPED 0xfffffffffffffffeull     // key of a box whose protected range does not fit the key's fields
+#define FB_SCREEN_MAX_W_STRICT 65536u
+#define FB_SCREEN_MAX_W_RELAXED 256u
+#define FB_SCREEN_MAX_THR 127
+
+// One sample.  ev(v, r) = logit with the protected column set to v and, in relaxed mode, the RA column to r.
+// Strict pairs first: the smallest protected value with a positive logit and the smallest with a negative one (low
+// word = off_pos << 16 | off_neg, offsets from pa_lo).  Relaxed mode, when the strict sweep shows one class only: the
+// first (delta ascending from -thr, protected value ascending) second point of the other class that has a partner of
+// a different protected value in the strict sweep (low word = off_pos << 24 | off_neg << 16 | (dpos+128) << 8 | (dneg+128),
+// d* = RA offset of that point, 0 for the one inside the partition).  0xffffffff: no counterexample in this sample.
+template <class Eval>
+__device__ __forceinline__ uint32_t fb_screen_sample(Eval &ev, int pa_lo, uint32_t W, bool relaxed, int ra_val, int thr)
+{
+    bool havep = false, haven = false;
+    int vp = 0, vn = 0, vp2 = -1, vn2 = -1;
+    for (uint32_t off = 0; off < W; ++off) {
+        const float y = ev(pa_lo + (int)off, ra_val);
+        if (y > 0.0f) { if (!havep) { havep = true; vp = (int)off; } else if (vp2 < 0) vp2 = (int)off; }
+        if (y < 0.0f) { if (!haven) { haven = true; vn = (int)off; } else if (vn2 < 0) vn2 = (int)off; }
+    }
+    if (havep && haven)
+        return relaxed ? ((uint32_t)vp << 24) | ((uint32_t)vn << 16) | (128u << 8) | 128u : ((uint32_t)vp << 16) | (uint32_t)vn;
+    if (relaxed && havep != haven) {
+        for (int d = -thr; d <= thr; ++d) {
+            if (d == 0) continue;
+            for (uint32_t off = 0; off < W; ++off) {
+                const float y = ev(pa_lo + (int)off, ra_val + d);
+                if (havep && y < 0.0f) {
+                    const int partner = (vp != (int)off) ? vp : vp2;
+                    if (partner >= 0) return ((uint32_t)partner << 24) | (off << 16) | (128u << 8) | (uint32_t)(d + 128);
+                }
+                if (haven && y > 0.0f) {
+                    const int partner = (vn != (int)off) ? vn : vn2;
+                    if (partner >= 0) return (off << 24) | ((uint32_t)partner << 16) | ((uint32_t)(d + 128) << 8) | 128u;
+                }
+            }
+        }
+    }
+    return 0xffffffffu;
+}
+
 template <class S, bool PHILOX>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS)
 fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int64_t n,
                                 const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
-                                int64_t first_index, int nsamp, int chunks, int chunk_len, int pa_col,
+                                int64_t first_index, int nsamp, int chunks, int chunk_len, int pa_col, int ra_col, int ra_thr,
                                 unsigned long long *__restrict__ ce_key)
 {
     constexpr int D0 = S::D0;
@@ -222,6 +269,7 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t units = n * chunks;
+    const bool relaxed = ra_col >= 0;
     for (int64_t u = gwarp; u < units; u += nwarps) {
         const int64_t p = u / chunks;
         const int c = (int)(u - p * chunks);
@@ -229,15 +277,20 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
         const int s1 = min(nsamp, s0 + chunk_len);
         int32_t lo[D0];
         uint32_t range[D0];
-        int pa_lo = 0, pa_hi = 0;
+        int pa_lo = 0;
+        uint32_t W = 0;
         {
             const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
 #pragma unroll
             for (int i = 0; i < D0; ++i) {
                 const int2 b = __ldg(bx + i);
                 lo[i] = b.x; range[i] = (uint32_t)(b.y - b.x + 1);
-                if (i == pa_col) { pa_lo = b.x; pa_hi = b.y; }
+                if (i == pa_col) { pa_lo = b.x; W = range[i]; }
             }
+        }
+        if (W == 0 || W > (relaxed ? FB_SCREEN_MAX_W_RELAXED : FB_SCREEN_MAX_W_STRICT)) {    // (W == 0: a 2^32-wide range)
+            if (lane == 0 && c == 0) ce_key[p] = FB_SCREEN_SKIPPED;
+            continue;
         }
         uint32_t widest = 0;
 #pragma unroll
@@ -258,21 +311,20 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
 #pragma unroll
                 for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);
             }
-            bool havep = false, haven = false;
-            int vp = 0, vn = 0;
-            FbReluVisit<float> vis;
-            for (int v = pa_lo; v <= pa_hi; ++v) {
+            int ra_val = 0;
+#pragma unroll
+            for (int i = 0; i < D0; ++i)
+                if (i == ra_col) ra_val = (int)x0[i];
+            auto ev = [&](int v, int r) {
                 float x[D0];
 #pragma unroll
-                for (int i = 0; i < D0; ++i) x[i] = (i == pa_col) ? (float)v : x0[i];
-                const float y = fb_spec_forward<S, 0, float>(prm, x, vis);
-                if (y > 0.0f && !havep) { havep = true; vp = v; }
-                if (y < 0.0f && !haven) { haven = true; vn = v; }
-            }
-            const bool ce = active && havep && haven;
-            if (ce && best == ~0ull)
-                best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)(vp - pa_lo) << 16) |
-                       (unsigned long long)(uint32_t)(vn - pa_lo);
+                for (int i = 0; i < D0; ++i) x[i] = (i == pa_col) ? (float)v : ((i == ra_col) ? (float)r : x0[i]);
+                FbReluVisit<float> vis;
+                return fb_spec_forward<S, 0, float>(prm, x, vis);
+            };
+            const uint32_t low = fb_screen_sample(ev, pa_lo, W, relaxed, ra_val, ra_thr);
+            const bool ce = active && low != 0xffffffffu;
+            if (ce && best == ~0ull) best = ((unsigned long long)(uint32_t)s << 32) | low;
             if (__any_sync(0xffffffffu, ce)) break;          // later samples cannot beat this step's
         }
         // lowest sample index wins; keys are unique per sample so min over the packed key is enough
@@ -281,4 +333,3 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
         if (hmin != 0xffffffffu && hi == hmin) atomicMin(&ce_key[p], best);
     }
 }
-

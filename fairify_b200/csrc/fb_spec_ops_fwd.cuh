@@ -64,18 +64,19 @@ struct FbSpecFwdOps {
 
     static cudaError_t partition_screen(const void *p32, bool philox, int64_t n, const int32_t *boxes,
                                         const int32_t *samples, uint64_t seed, int64_t first_index, int nsamp, int chunks,
-                                        int chunk_len, int pa_col, unsigned long long *ce_key, int num_sms, cudaStream_t st)
+                                        int chunk_len, int pa_col, int ra_col, int ra_thr, unsigned long long *ce_key, int num_sms,
+                                        cudaStream_t st)
     {
         const P32 &prm = *static_cast<const P32 *>(p32);
         const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
         if (philox) {
             auto k = fb_partition_screen_spec_kernel<S, true>;
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ce_key);
+                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ra_col, ra_thr, ce_key);
         } else {
             auto k = fb_partition_screen_spec_kernel<S, false>;
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ce_key);
+                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ra_col, ra_thr, ce_key);
         }
         return cudaGetLastError();
     }

@@ -19,22 +19,26 @@ def shard_range(n_total, rank, world):
 
 
 def record_width(NW):
-    return 1 + 2 * NW
+    """uint32 words per partition in the packed record fb_ibp writes (include/fairify_b200.h, fb_prune_out.record):
+    verdict flags | dead-mask words | candidate-mask words | first counterexample sample (-1 = none)."""
+    return 2 * NW + 2
 
 
-def pack_records(verdict, dead, cand, out=None):
-    """int32 [n, 1 + 2*NW]: verdict byte, dead-mask words, candidate-mask words."""
+def pack_records(verdict, dead, cand, ce=None, out=None):
+    """The same record assembled from separate tensors (host-side tests; on the device fb_ibp writes it directly)."""
     n, NW = dead.shape
     if out is None:
         out = torch.empty((n, record_width(NW)), dtype=torch.int32, device=dead.device)
     out[:, 0] = verdict
     out[:, 1:1 + NW] = dead
-    out[:, 1 + NW:] = cand
+    out[:, 1 + NW:1 + 2 * NW] = cand
+    out[:, 1 + 2 * NW] = -1 if ce is None else ce
     return out
 
 
 def unpack_records(rec, NW):
-    return rec[:, 0].to(torch.uint8), rec[:, 1:1 + NW], rec[:, 1 + NW:]
+    """(verdict uint8, dead words, candidate words, first counterexample sample) views of [n, 2*NW+2] records."""
+    return rec[:, 0].to(torch.uint8), rec[:, 1:1 + NW], rec[:, 1 + NW:1 + 2 * NW], rec[:, 1 + 2 * NW]
 
 
 def allgather_records(local, n_total, group=None):
@@ -59,15 +63,17 @@ def allgather_records(local, n_total, group=None):
     return torch.cat(parts, dim=0) if any(shard_range(n_total, r, world)[1] != cmax for r in range(world)) else gathered
 
 
-def prune_grid_sharded(model, grid, S=1000, seed=0, tol=None, n_total=None, group=None):
-    """Every rank prunes its slice of the grid on its own GPU; returns (verdict, dead, cand) for ALL partitions
-    on every rank."""
+def prune_grid_sharded(model, grid, S=1000, seed=0, tol=None, n_total=None, group=None, pa_col=None):
+    """Every rank prunes (and, given a protected column, screens) its slice of the grid on its own GPU; returns
+    (verdict, dead, cand, first counterexample sample) for ALL partitions on every rank."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     n_total = len(grid) if n_total is None else int(n_total)
     first, count = shard_range(n_total, rank, world)
     boxes = grid.boxes(first, count)
-    r = model.prune(boxes, S=S, seed=seed, first_index=first, tol=tol, want=("cand", "dead", "verdict"))
-    rec = pack_records(r.t["verdict"], r.t["dead"], r.t["cand"])
+    r = model.prune(boxes, S=S, seed=seed, first_index=first, tol=tol, want=("record",))
+    rec = r.t["record"]
+    if pa_col is not None:
+        model.partition_screen(boxes, pa_col, S=S, seed=seed, first_index=first, record=rec)
     full = allgather_records(rec, n_total, group)
     return unpack_records(full, model.NW)

@@ -296,16 +296,54 @@ class Model:
                                         _ptr(alts), _ptr(orig), _ptr(flip), _stream()), "fb_pair_screen")
         return orig, flip
 
-    def partition_screen(self, boxes, pa_col, S=1000, samples=None, seed=0, first_index=0, verdict=None):
+    def partition_screen(self, boxes, pa_col, S=1000, samples=None, seed=0, first_index=0, verdict=None, ra_col=None,
+                         ra_threshold=0, record=None):
+        """Sampled counterexample screen.  Returns [ce_sample, pa_pos, pa_neg] (int32 [n] each), plus [ra_dpos, ra_dneg]
+        when a relaxed column is given (relaxed/AC/Verify-AC.py:48-51); `record` = the packed records of prune()."""
         boxes = self._dev(boxes, torch.int32); n = boxes.shape[0]
         samples = self._dev(samples, torch.int32)
         if samples is not None:
             S = samples.shape[1]
-        outs = [torch.empty((n,), dtype=torch.int32, device=self.device) for _ in range(3)]
-        check(_lib.lib().fb_partition_screen(self._h, n, _ptr(boxes), _ptr(samples), int(S), C.c_uint64(seed),
-                                             int(first_index), int(pa_col), _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]),
-                                             _ptr(verdict), _stream()), "fb_partition_screen")
+        relaxed = ra_col is not None and ra_col >= 0
+        outs = [torch.empty((n,), dtype=torch.int32, device=self.device) for _ in range(5 if relaxed else 3)]
+        check(_lib.lib().fb_partition_screen_ex(self._h, n, _ptr(boxes), _ptr(samples), int(S), C.c_uint64(seed),
+                                                int(first_index), int(pa_col), int(ra_col) if relaxed else -1, int(ra_threshold),
+                                                _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(outs[3]) if relaxed else None,
+                                                _ptr(outs[4]) if relaxed else None, _ptr(verdict), _ptr(record), _stream()),
+              "fb_partition_screen")
         return outs
+
+    def nearzero(self, boxes, S=1000, samples=None, seed=0, first_index=0):
+        """(count, smallest ratio) of |pre-activation| / (sum |w x| + |b|) over every sample and neuron of the batch
+        (fb_profile_nearzero): how far the activation signs are from depending on the summation order."""
+        boxes = self._dev(boxes, torch.int32); n = boxes.shape[0]
+        samples = self._dev(samples, torch.int32)
+        if samples is not None:
+            S = samples.shape[1]
+        cnt = torch.zeros((1,), dtype=torch.int64, device=self.device)
+        best = torch.ones((1,), dtype=torch.float64, device=self.device)
+        check(_lib.lib().fb_profile_nearzero(self._h, n, _ptr(boxes), _ptr(samples), int(S), C.c_uint64(seed), int(first_index),
+                                             _ptr(cnt), _ptr(best), _stream()), "fb_profile_nearzero")
+        return int(cnt.item()), float(best.item())
+
+
+STATUS = {None: 0, "none": 0, "sat": 1, "unsat": 2, "unknown": 3}
+
+
+def hybrid_predict(grid, original, fairer, X, status):
+    """find_partition_result_for_point + hybrid_predict (src/AC/Verify-AC-experiment-new2.py:587-638) for all rows of X at
+    once: (float32 logits of the model each row's partition verdict selects, route uint8 [rows], counters int32 [4]).
+    status: uint8 [grid size] of STATUS codes (0 = partition not evaluated)."""
+    X = np.ascontiguousarray(X)
+    x64 = torch.as_tensor(X.astype(np.float64)).to(grid.device); x32 = torch.as_tensor(X.astype(np.float32)).to(grid.device)
+    st = status if isinstance(status, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(status, dtype=np.uint8)).to(grid.device)
+    rows = x64.shape[0]
+    logit = torch.empty((rows,), dtype=torch.float32, device=grid.device)
+    route = torch.empty((rows,), dtype=torch.uint8, device=grid.device)
+    counters = torch.zeros((4,), dtype=torch.int32, device=grid.device)
+    check(_lib.lib().fb_hybrid_predict(grid._h, original._h, fairer._h, rows, _ptr(x64), _ptr(x32), _ptr(st), _ptr(logit),
+                                       _ptr(route), _ptr(counters), _stream()), "fb_hybrid_predict")
+    return logit, route, counters
 
 
 class Grid:

@@ -41,6 +41,7 @@ extern "C" {
 #define FB_VERDICT_CERTIFIED 1u /* logit provably > 0 or < 0 on the whole box: no counterexample exists */
 #define FB_VERDICT_CE 2u        /* the sampled screen found a counterexample pair */
 #define FB_VERDICT_SLIVER 4u    /* a bound is within rounding error of 0: host must run the Z3 neuron check */
+#define FB_VERDICT_SKIPPED 8u   /* the partition screen skipped this box: its protected range does not fit the limits below */
 
 typedef struct fb_model fb_model;
 typedef struct fb_grid fb_grid;
@@ -153,10 +154,50 @@ int fb_pair_screen(const fb_model *m, int64_t rows, const float *X, int n_pa, co
 
 /* -- per-partition sampled counterexample screen (the property src/AC/Verify-AC.py:137-156 gives Z3).
  *    ce_sample/pa_pos/pa_neg int32 [n]: lowest sample index that is a counterexample and the protected
- *    values with logit > 0 / < 0, or -1.  verdict (may be NULL) gets FB_VERDICT_CE OR-ed in. */
+ *    values with logit > 0 / < 0, or -1.  verdict (may be NULL) gets FB_VERDICT_CE OR-ed in.
+ *    (fb_partition_screen_ex below with ra_col = -1 and no record.) */
 int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                         uint64_t seed, int64_t first_index, int pa_col, int32_t *ce_sample, int32_t *pa_pos,
                         int32_t *pa_neg, uint8_t *verdict, void *stream);
+
+/* Same screen with every option.
+ *    Limits: the protected column's range hi - lo + 1 of a box may be at most 65 536 values (256 with a relaxed column);
+ *    a box beyond that is skipped and marked FB_VERDICT_SKIPPED in verdict / record.
+ *    ra_col >= 0 selects the RELAXED query of relaxed/AC/Verify-AC.py:48-51, :128-132 (in_const_diff_adult,
+ *    utils/verif_utils.py:859-867): the two points may also differ in column ra_col by at most ra_threshold (0..127).
+ *    As in the reference, only the first point must lie in the box (in_const_domain_* bounds x' on the protected columns
+ *    alone, :846-854): the second point's ra value ranges over a - thr .. a + thr around the sample's value a.
+ *    A strict pair (difference 0) is preferred; otherwise the first second point -- difference ascending from -thr,
+ *    protected value ascending -- with a partner of another protected value and the other class.
+ *    ra_dpos / ra_dneg int32 [n] (may be NULL): the difference applied to the positive / negative point (0 for the point
+ *    inside the box).  Any of ce_sample / pa_pos / pa_neg / verdict may be NULL.  record (may be NULL): the packed records
+ *    fb_ibp wrote ([n][2*NW+2] uint32): the last word of each receives ce_sample, word 0 the verdict flags. */
+int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
+                           uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_threshold,
+                           int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg,
+                           uint8_t *verdict, uint32_t *record, void *stream);
+
+/* -- hybrid prediction: find_partition_result_for_point + hybrid_predict, src/AC/Verify-AC-experiment-new2.py:587-638.
+ *    For each of `rows` points: the partition of grid g that contains it, that partition's recorded verdict
+ *    status[index] (uint8 [grid size]: FB_STATUS_NONE = not evaluated, _SAT, _UNSAT, _UNKNOWN), and the float32 logit
+ *    of the model the verdict selects: `fairer` where the partition is unfair (SAT), `original` everywhere else (also
+ *    for points outside every partition).  X64 float64 [rows][d] (located) and X32 float32 [rows][d] (predicted) hold the
+ *    same points.  logit float32 [rows]; route uint8 [rows] (may be NULL) = the status that decided; counters uint32 [4]
+ *    (may be NULL) += number of rows per status (the reference's debug_counters). */
+#define FB_STATUS_NONE 0
+#define FB_STATUS_SAT 1
+#define FB_STATUS_UNSAT 2
+#define FB_STATUS_UNKNOWN 3
+int fb_hybrid_predict(const fb_grid *g, const fb_model *original, const fb_model *fairer, int64_t rows, const double *X64,
+                      const float *X32, const uint8_t *status, float *logit, uint8_t *route, uint32_t *counters, void *stream);
+
+/* -- diagnostic: how close the sampled pre-activations come to zero.  The reference's forward pass sums through numpy's
+ *    BLAS in an unspecified order (utils/AC-1-Model-Functions.py:19); every kernel here sums in ascending input order.
+ *    A sign -- all the activation profile consumes -- can differ between the two only where |pre-activation| is within
+ *    rounding error of sum |w x| + |b|.  count (device uint64) = number of (sample, neuron) pairs of the batch with
+ *    |pre| <= 2^-40 (sum |w x| + |b|); min_ratio (device double) = the smallest such ratio seen.  Not a fast path. */
+int fb_profile_nearzero(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
+                        int64_t first_index, uint64_t *count, double *min_ratio, void *stream);
 
 /* -- heuristic_prune, utils/prune.py:862-939 (only reached after a Z3 `unknown`): per hidden layer compare the
  *    ws_ub of sample-candidates and non-candidates (numpy mean / median / percentile semantics) and mark small-bound

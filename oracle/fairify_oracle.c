@@ -711,6 +711,94 @@ void fo_partition_screen(int L, const int32_t *dims, const float *W32, const flo
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * The same screen with the RELAXED query of relaxed/AC/Verify-AC.py:48-51, :128-132: the two points may also differ
+ * in column ra_col by at most thr (in_const_diff_adult, utils/verif_utils.py:859-867).  Only the first point has to
+ * lie in the partition (in_const_domain_adult bounds x' on the protected columns alone, :846-854), so the second
+ * point's ra value ranges over a - thr .. a + thr around the sample's value a, unclipped.  Per sample: the strict
+ * sweep first (smallest protected value with a positive logit, smallest with a negative one); if it shows one class
+ * only, the first second point -- difference d ascending from -thr (d != 0), protected value ascending -- of the
+ * other class that has a partner with a different protected value in the strict sweep.  ra_col < 0: strict only.
+ * ra_dpos / ra_dneg: the difference applied to the positive / negative point (0 for the one inside the box).
+ * ---------------------------------------------------------------------------------------------- */
+void fo_partition_screen_ex(int L, const int32_t *dims, const float *W32, const float *B32, int64_t n,
+                            int S, const int32_t *samples, const int32_t *boxes, int pa_col, int ra_col, int thr,
+                            int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg)
+{
+    int d = dims[0], mw = fo_maxw(L, dims);
+#pragma omp parallel
+    {
+        float *buf = (float *)malloc(sizeof(float) * (mw * 3 + d));
+        float *x = buf + mw * 3;
+#pragma omp for schedule(static)
+        for (int64_t p = 0; p < n; ++p) {
+            int lo = boxes[(p * d + pa_col) * 2], hi = boxes[(p * d + pa_col) * 2 + 1];
+            ce_sample[p] = -1; pa_pos[p] = -1; pa_neg[p] = -1; ra_dpos[p] = 0; ra_dneg[p] = 0;
+            for (int s = 0; s < S && ce_sample[p] < 0; ++s) {
+                const int32_t *xi = samples + (p * S + s) * d;
+                for (int i = 0; i < d; ++i) x[i] = (float)xi[i];
+                int vp = -1, vn = -1, vp2 = -1, vn2 = -1;
+                for (int v = lo; v <= hi; ++v) {
+                    memcpy(buf, x, sizeof(float) * d);
+                    buf[pa_col] = (float)v;
+                    float y = fo_logit_f32(L, dims, W32, B32, buf, buf + mw, buf + 2 * mw);
+                    if (y > 0) { if (vp < 0) vp = v; else if (vp2 < 0) vp2 = v; }
+                    if (y < 0) { if (vn < 0) vn = v; else if (vn2 < 0) vn2 = v; }
+                }
+                if (vp >= 0 && vn >= 0) { ce_sample[p] = s; pa_pos[p] = vp; pa_neg[p] = vn; continue; }
+                if (ra_col < 0 || (vp < 0) == (vn < 0)) continue;
+                for (int dd = -thr; dd <= thr && ce_sample[p] < 0; ++dd) {
+                    if (dd == 0) continue;
+                    for (int v = lo; v <= hi && ce_sample[p] < 0; ++v) {
+                        memcpy(buf, x, sizeof(float) * d);
+                        buf[pa_col] = (float)v; buf[ra_col] = (float)(xi[ra_col] + dd);
+                        float y = fo_logit_f32(L, dims, W32, B32, buf, buf + mw, buf + 2 * mw);
+                        if (vp >= 0 && y < 0) {
+                            int partner = (vp != v) ? vp : vp2;
+                            if (partner >= 0) { ce_sample[p] = s; pa_pos[p] = partner; pa_neg[p] = v; ra_dneg[p] = dd; }
+                        } else if (vn >= 0 && y > 0) {
+                            int partner = (vn != v) ? vn : vn2;
+                            if (partner >= 0) { ce_sample[p] = s; pa_pos[p] = v; pa_neg[p] = partner; ra_dpos[p] = dd; }
+                        }
+                    }
+                }
+            }
+        }
+        free(buf);
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Diagnostic of the summation-order question (see fb_profile_nearzero in include/fairify_b200.h): per (sample, neuron)
+ * the ratio |pre| / (sum |w x| + |b|); count of ratios <= 2^-40 and the smallest ratio.
+ * ---------------------------------------------------------------------------------------------- */
+void fo_nearzero(int L, const int32_t *dims, const double *W, const double *B, int64_t n, int S, const int32_t *samples,
+                 uint64_t *count, double *min_ratio)
+{
+    fo_net m; if (fo_net_init(&m, L, dims, W, B)) return;
+    int d = dims[0];
+    uint64_t cnt = 0; double best = 1.0;
+    double *a = (double *)malloc(sizeof(double) * m.maxw * 2), *y = a + m.maxw;
+    for (int64_t u = 0; u < n * S; ++u) {
+        for (int i = 0; i < d; ++i) a[i] = (double)samples[u * d + i];
+        double *in = a, *out = y;
+        for (int l = 0; l < L; ++l) {
+            int IN = dims[l], OUT = dims[l + 1];
+            const double *w = W + m.woff[l], *b = B + m.boff[l];
+            for (int j = 0; j < OUT; ++j) {
+                double acc = 0.0, mag = 0.0;
+                for (int i = 0; i < IN; ++i) { acc = fma(w[(int64_t)i * OUT + j], in[i], acc); mag = fma(fabs(w[(int64_t)i * OUT + j]), fabs(in[i]), mag); }
+                double pre = acc + b[j]; mag = mag + fabs(b[j]);
+                if (mag > 0.0) { double r = fabs(pre) / mag; if (r <= 0x1p-40) ++cnt; if (r < best) best = r; }
+                out[j] = (l == L - 1) ? pre : (pre > 0.0 ? pre : 0.0);
+            }
+            double *t = in; in = out; out = t;
+        }
+    }
+    free(a);
+    *count = cnt; *min_ratio = best;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * Whole pre-solver for a batch of boxes (a3 Philox + a5 + a6 + a7 + a8 + a10), used as the timed CPU
  * baseline and as the end-to-end checker of the fused device path.  Outputs: counts [n][N] and the
  * byte masks of fo_masks, plus the verdict byte: bit0 = output logit provably > 0 or < 0 over the

@@ -179,6 +179,35 @@ def partition_screen(net, samples, boxes, pa_col):
     return outs
 
 
+def partition_screen_ex(net, samples, boxes, pa_col, ra_col=-1, thr=0):
+    """(ce_sample, pa_pos, pa_neg, ra_dpos, ra_dneg): the screen with the relaxed query (fo_partition_screen_ex)."""
+    samples = np.ascontiguousarray(samples, dtype=np.int32); boxes = np.ascontiguousarray(boxes, dtype=np.int32)
+    n, S = samples.shape[0], samples.shape[1]
+    outs = [np.zeros(n, dtype=np.int32) for _ in range(5)]
+    lib().fo_partition_screen_ex(net.L, _p(net.dims), _p(net.W32), _p(net.B32), C.c_int64(n), S, _p(samples), _p(boxes),
+                                 int(pa_col), int(ra_col), int(thr), *[_p(o) for o in outs])
+    return outs
+
+
+def nearzero(net, samples):
+    """(count of (sample, neuron) pairs with |pre| <= 2^-40 (sum |w x| + |b|), smallest ratio)."""
+    samples = np.ascontiguousarray(samples, dtype=np.int32); n, S = samples.shape[0], samples.shape[1]
+    cnt = C.c_uint64(); best = C.c_double()
+    lib().fo_nearzero(net.L, _p(net.dims), _p(net.W), _p(net.B), C.c_int64(n), S, _p(samples), C.byref(cnt), C.byref(best))
+    return int(cnt.value), float(best.value)
+
+
+def hybrid_predict(original, fairer, lo, hi, T, key_order, X, status):
+    """find_partition_result_for_point + hybrid_predict (src/AC/Verify-AC-experiment-new2.py:587-638) restated:
+    (float32 logit of the selected model, route = status that decided) per row of X."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    idx = grid_locate(lo, hi, T, key_order, X)
+    st = np.where(idx >= 0, np.asarray(status, dtype=np.uint8)[np.maximum(idx, 0)], 0).astype(np.uint8)
+    st = np.where(st <= 3, st, 0).astype(np.uint8)
+    yo = forward_f32(original, X.astype(np.float32)); yf = forward_f32(fairer, X.astype(np.float32))
+    return np.where(st == 1, yf, yo).astype(np.float32), st
+
+
 def prune_batch(net, boxes, seed, first_index, S, tol):
     boxes = np.ascontiguousarray(boxes, dtype=np.int32); n = boxes.shape[0]
     tol = np.ascontiguousarray(tol, dtype=np.float64)

@@ -443,8 +443,82 @@ def sliver_case():
     print("sliver case: seed", seed, "cand", flat_u8(cand), "s_dead", flat_u8(s_dead), "dead", flat_u8(dead))
 
 
+def hybrid_case():
+    """hybrid_predict / find_partition_result_for_point of src/AC/Verify-AC-experiment-new2.py:587-638, taken out of
+    that script at generation time (it is a module-level program, not importable) and run on a random verdict table:
+    python tests/golden/make_golden.py hybrid  ->  tests/golden/hybrid_case.npz"""
+    import ast
+    path = os.path.join(REF, "src", "AC", "Verify-AC-experiment-new2.py")
+    tree = ast.parse(open(path).read())
+    wanted = ("partition_to_key", "key_to_partition", "find_partition_result_for_point", "hybrid_predict")
+    ns = {"np": np}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in wanted:
+            exec(compile(ast.Module([node], []), path, "exec"), ns)
+    assert all(k in ns for k in wanted)
+    ref = refshim.load()
+    weights = np.load(os.path.join(HERE, "weights.npz"))
+    D = domains.DOMAINS["AC"]
+
+    class Net:          # what hybrid_predict uses of a keras model: predict(x[1, d]) -> sigmoid outputs, float32 Dense stack
+        def __init__(self, name):
+            L = int(weights[f"{name}/L"])
+            self.w = [weights[f"{name}/w{l}"] for l in range(L)]; self.b = [weights[f"{name}/b{l}"] for l in range(L)]
+            self.logits = []
+
+        def predict(self, x, verbose=0):
+            x = np.asarray(x, dtype=np.float32)
+            for l in range(len(self.w)):
+                x = x @ self.w[l] + self.b[l]
+                if l < len(self.w) - 1:
+                    x = np.maximum(x, np.float32(0))
+            self.last_logit = np.float32(x[0][0])
+            return np.float32(1) / (np.float32(1) + np.exp(-x, dtype=np.float32))
+
+    orig, fair = Net("AC-3"), Net("AC-1")
+    rd = D.copy_ranges()
+    T = 10
+    p_dict = ref.input_partition.partition(rd, T)
+    p_list = ref.input_partition.partitioned_ranges(rd.keys(), D.pa, p_dict, rd)
+    rng = np.random.RandomState(21)
+    status = np.zeros(len(p_list), dtype=np.uint8)
+    names = {1: "sat", 2: "unsat", 3: "unknown"}
+    partition_results = {}
+    lo = np.array([rd[c][0] for c in D.columns]); hi = np.array([rd[c][1] for c in D.columns])
+    X = rng.randint(lo, hi + 1, size=(300, D.d)).astype(np.float64)
+    X[::29, 0] = 5.0                                   # below the age range: in no partition
+    # verdicts for the partitions the points fall in (two thirds of them) and for some others
+    boxes = np.stack([box_array(p, D.columns) for p in p_list])
+    for r in range(X.shape[0]):
+        inside = np.all((X[r] >= boxes[:, :, 0]) & (X[r] <= boxes[:, :, 1]), axis=1)
+        k = np.flatnonzero(inside)
+        if len(k) and r % 3 != 0:
+            status[k[0]] = rng.randint(1, 4)
+    extra = rng.choice(len(p_list), 200, replace=False)
+    status[extra] = np.where(status[extra] == 0, rng.randint(1, 4, size=200), status[extra])
+    for k in np.flatnonzero(status):
+        partition_results[ns["partition_to_key"](p_list[k])] = names[int(status[k])]
+    import collections
+    counters = collections.defaultdict(int)
+    preds, logits, routes = [], [], []
+    for r in range(X.shape[0]):
+        st, key = ns["find_partition_result_for_point"](X[r], partition_results)
+        pred = ns["hybrid_predict"](X[r], orig, fair, partition_results, counters, "AC-3", "AC-1")
+        used = fair if st == "sat" else orig
+        preds.append(np.float32(pred)); logits.append(used.last_logit)
+        routes.append({None: 0, "sat": 1, "unsat": 2, "unknown": 3}[st])
+    out = {"X": X, "status": status, "T": np.int64(T), "pred": np.array(preds, dtype=np.float32),
+           "logit": np.array(logits, dtype=np.float32), "route": np.array(routes, dtype=np.uint8),
+           "counters": np.array([counters["fallback_to_original"], counters["sat_unfair_ac-1_used"],
+                                 counters["unsat_fair_ac-3_used"], counters["unknown_ac-3_used"]], dtype=np.int64)}
+    np.savez_compressed(os.path.join(HERE, "hybrid_case.npz"), **out)
+    print("hybrid case: routes", np.bincount(out["route"], minlength=4), "counters", out["counters"])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "singular":
+    if len(sys.argv) > 1 and sys.argv[1] == "hybrid":
+        hybrid_case()
+    elif len(sys.argv) > 1 and sys.argv[1] == "singular":
         singular_cases()
     elif len(sys.argv) > 1 and sys.argv[1] == "sliver":
         sliver_case()

@@ -28,7 +28,8 @@ def _fake_records(first, count, NW):
     verdict = (idx % 5).to(torch.uint8)
     dead = torch.stack([(idx * (k + 3) % 65521).to(torch.int32) for k in range(NW)], dim=1)
     cand = torch.stack([(idx * (k + 11) % 32749).to(torch.int32) for k in range(NW)], dim=1)
-    return verdict, dead, cand
+    ce = ((idx * 7) % 1001 - 1).to(torch.int32)
+    return verdict, dead, cand, ce
 
 
 def _worker(rank, world, port, n_total, NW, ret):
@@ -36,11 +37,11 @@ def _worker(rank, world, port, n_total, NW, ret):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         first, count = shard_range(n_total, rank, world)
-        v, d, c = _fake_records(first, count, NW)
-        full = allgather_records(pack_records(v, d, c), n_total)
-        gv, gd, gc = unpack_records(full, NW)
-        ev, ed, ec = _fake_records(0, n_total, NW)
-        ok = bool(torch.equal(gv, ev) and torch.equal(gd, ed) and torch.equal(gc, ec))
+        v, d, c, e = _fake_records(first, count, NW)
+        full = allgather_records(pack_records(v, d, c, e), n_total)
+        gv, gd, gc, ge = unpack_records(full, NW)
+        ev, ed, ec, ee = _fake_records(0, n_total, NW)
+        ok = bool(torch.equal(gv, ev) and torch.equal(gd, ed) and torch.equal(gc, ec) and torch.equal(ge, ee))
         ret[rank] = ok
     finally:
         dist.destroy_process_group()

@@ -413,6 +413,98 @@ def test_partition_screen_matches_oracle(eng, name):
             assert ya > 0 and yb < 0
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-3", "AC-5", "AC-4", "AC-10"])
+def test_relaxed_partition_screen_matches_oracle(eng, name):
+    """relaxed/AC query (PA = race, RA = age, threshold 5; relaxed/AC/Verify-AC.py:48-51): counterexample sample, protected
+    values and the difference applied to the relaxed column, bit for bit against the oracle; every reported pair is
+    re-checked to flip the float32 class; with no relaxed column the answers are those of the strict screen."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    pa, ra, thr = dom.columns.index("race"), dom.columns.index("age"), 5
+    grid = eng.Grid(dom.columns, dom.ranges, 6)                    # stress / relaxed grid of the Adult drivers
+    first = len(grid) // 3
+    n = 48 if m.P > 4000 else 160
+    boxes = grid.boxes(first, n); hb = boxes.cpu().numpy()
+    S = 70
+    samples = O.philox_samples(11, first, hb, S)
+    want = O.partition_screen_ex(net, samples, hb, pa, ra, thr)
+    verdict = torch.zeros((n,), dtype=torch.uint8, device="cuda")
+    got = m.partition_screen(boxes, pa, S=S, seed=11, first_index=first, ra_col=ra, ra_threshold=thr, verdict=verdict)
+    for g_, w_, key in zip(got, want, ("ce_sample", "pa_pos", "pa_neg", "ra_dpos", "ra_dneg")):
+        assert np.array_equal(g_.cpu().numpy(), w_), key
+    ce = want[0]
+    assert np.array_equal((verdict.cpu().numpy() & eng.VERDICT_CE) != 0, ce >= 0)
+    for p in np.flatnonzero(ce >= 0)[:40]:
+        x = samples[p, ce[p]].astype(np.float32)
+        xp = x.copy(); xp[pa] = want[1][p]; xp[ra] += want[3][p]
+        xn = x.copy(); xn[pa] = want[2][p]; xn[ra] += want[4][p]
+        y = m.forward(np.stack([xp, xn])).cpu().numpy()
+        assert y[0] > 0 > y[1]
+    # injected samples give the same; no relaxed column = the strict screen
+    got2 = m.partition_screen(boxes, pa, samples=samples, ra_col=ra, ra_threshold=thr)
+    assert all(np.array_equal(a.cpu().numpy(), b_) for a, b_ in zip(got2, want))
+    strict = m.partition_screen(boxes, pa, S=S, seed=11, first_index=first)
+    assert np.array_equal(strict[0].cpu().numpy(), O.partition_screen(net, samples, hb, pa)[0])
+    assert (ce >= 0).sum() >= (strict[0].cpu().numpy() >= 0).sum()
+
+
+def test_partition_screen_rejects_what_it_cannot_encode(eng):
+    """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
+    w, b = G.wb("GC-1")
+    m = eng.Model(w, b); dom = G.domain("GC-1")
+    col = dom.columns.index("credit_amount")                                   # range 0 .. 20000
+    box = np.array([[dom.ranges[c][0], dom.ranges[c][1]] for c in dom.columns], dtype=np.int32)[None].repeat(3, 0)
+    box[1, col] = [0, 70000]                                                   # 70 001 values: beyond 65 536
+    box[2, col] = [-2**31, 2**31 - 1]                                          # the whole int32 range
+    verdict = torch.zeros((3,), dtype=torch.uint8, device="cuda")
+    ce = m.partition_screen(box, col, S=8, seed=1, verdict=verdict)[0].cpu().numpy()
+    v = verdict.cpu().numpy()
+    assert (v[0] & 8) == 0 and (v[1] & 8) and (v[2] & 8) and ce[1] == -1 and ce[2] == -1
+    v2 = torch.zeros((3,), dtype=torch.uint8, device="cuda")
+    m.partition_screen(box, col, S=8, seed=1, verdict=v2, ra_col=0, ra_threshold=2)     # relaxed: 256 values at most
+    assert (v2.cpu().numpy() & 8).all()
+    with pytest.raises(Exception):
+        m.partition_screen(box, col, S=8, ra_col=col, ra_threshold=2)          # relaxed column == protected column
+    with pytest.raises(Exception):
+        m.partition_screen(box, col, S=8, ra_col=1, ra_threshold=500)
+
+
+def test_hybrid_predict_matches_reference_functions(eng):
+    """find_partition_result_for_point + hybrid_predict (src/AC/Verify-AC-experiment-new2.py:587-638) on the fixture the
+    reference's own functions produced: which model answers each point, the debug counters, the class of every point."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "hybrid_case.npz"))
+    dom = G.domain("AC-1")
+    grid = eng.Grid(dom.columns, dom.ranges, int(z["T"]))
+    orig, fair = eng.Model(*G.wb("AC-3")), eng.Model(*G.wb("AC-1"))
+    logit, route, counters = eng.hybrid_predict(grid, orig, fair, z["X"], z["status"])
+    logit = logit.cpu().numpy()
+    assert np.array_equal(route.cpu().numpy(), z["route"])
+    assert np.array_equal(counters.cpu().numpy(), z["counters"])
+    assert np.array_equal(logit > 0, z["pred"] > 0.5)
+    assert np.allclose(logit, z["logit"], rtol=2e-4, atol=2e-4)   # float32: numpy sums through BLAS, the oracle in index order
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    ko = np.array([dom.columns.index(k) for k in dom.ranges.keys()], dtype=np.int32)
+    want, _ = O.hybrid_predict(O.Net(*G.wb("AC-3")), O.Net(*G.wb("AC-1")), lo, hi, int(z["T"]), ko, z["X"], z["status"])
+    assert np.array_equal(logit, want)
+
+
+def test_nearzero_diagnostic(eng):
+    """fb_profile_nearzero equals the oracle on fixtures, and on the full src/AC grid (16 000 boxes x 1000 samples) no
+    pre-activation is within 2^-40 of its terms: the activation counts do not depend on the summation order."""
+    for name in ("AC-1", "GC-4", "BM-7"):
+        m = eng.Model(*G.wb(name)); net = O.Net(*G.wb(name))
+        cs = list(G.cases(name))[:2]
+        for c in cs:
+            got = m.nearzero(c["box"][None], samples=c["samples"][None])
+            want = O.nearzero(net, c["samples"][None])
+            assert got[0] == want[0] == 0 and got[1] == want[1], (name, got, want)
+    m = eng.Model(*G.wb("AC-1")); dom = G.domain("AC-1")
+    grid = eng.Grid(dom.columns, dom.ranges, 10)
+    cnt, best = m.nearzero(grid.boxes(), S=1000, seed=2024)
+    assert cnt == 0 and best > 2.0 ** -40, (cnt, best)
+
+
 def test_prune_host_roundtrip_equals_device(eng):
     w, b = G.wb("AC-1")
     m = eng.Model(w, b)
@@ -529,13 +621,16 @@ def _two_rank_worker(rank, world, port, ret):
             pass
         import fairify_b200.dist as D
         first, count = D.shard_range(len(grid), rank, world)
-        r = m.prune(grid.boxes(first, count), S=64, seed=5, first_index=first, want=("cand", "dead", "verdict"))
-        rec = D.pack_records(r.t["verdict"], r.t["dead"], r.t["cand"]).cpu()
-        full = D.allgather_records(rec, len(grid))
-        v, d, c = D.unpack_records(full, m.NW)
+        pa = dom.columns.index(dom.pa[0])
+        bx = grid.boxes(first, count)
+        r = m.prune(bx, S=64, seed=5, first_index=first, want=("record",))
+        m.partition_screen(bx, pa, S=64, seed=5, first_index=first, record=r.t["record"])
+        full = D.allgather_records(r.t["record"].cpu(), len(grid))
+        v, d, c, ce = D.unpack_records(full, m.NW)
         one = m.prune(grid.boxes(), S=64, seed=5, first_index=0, want=("cand", "dead", "verdict"))
+        one_ce = m.partition_screen(grid.boxes(), pa, S=64, seed=5, first_index=0, verdict=one.t["verdict"])[0]
         ok = (np.array_equal(v.numpy(), one.numpy("verdict")) and np.array_equal(d.numpy(), one.numpy("dead"))
-              and np.array_equal(c.numpy(), one.numpy("cand")))
+              and np.array_equal(c.numpy(), one.numpy("cand")) and np.array_equal(ce.numpy(), one_ce.cpu().numpy()))
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()

@@ -279,3 +279,81 @@ def test_constructed_sliver_case_is_flagged():
     assert m["sliver"][0][0] == 1 and m["sliver"][0].sum() == 1
     for k in ("cand", "b_dead", "s_dead", "s_cand", "dead"):
         assert np.array_equal(m[k][0], z[k]), k
+
+
+def test_hybrid_predict_matches_reference_functions():
+    """tests/golden/hybrid_case.npz: find_partition_result_for_point + hybrid_predict of
+    src/AC/Verify-AC-experiment-new2.py:587-638 on 300 points and a random verdict table (original AC-3, fairer AC-1)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "hybrid_case.npz"))
+    dom = G.domain("AC-1")
+    lo = np.array([dom.ranges[c][0] for c in dom.columns]); hi = np.array([dom.ranges[c][1] for c in dom.columns])
+    ko = np.array([dom.columns.index(k) for k in dom.ranges.keys()], dtype=np.int32)
+    orig, fair = O.Net(*G.wb("AC-3")), O.Net(*G.wb("AC-1"))
+    logit, route = O.hybrid_predict(orig, fair, lo, hi, int(z["T"]), ko, z["X"], z["status"])
+    assert np.array_equal(route, z["route"])
+    assert np.array_equal(np.bincount(route, minlength=4), z["counters"])
+    assert np.array_equal(logit > 0, z["logit"] > 0) and np.allclose(logit, z["logit"], rtol=2e-4, atol=2e-4)   # float32: numpy sums through BLAS, the oracle in index order
+    assert np.array_equal(logit > 0, z["pred"] > 0.5)
+
+
+def test_relaxed_screen_restatement():
+    """The relaxed screen against a brute-force enumeration of the property the relaxed drivers give Z3
+    (relaxed/AC/Verify-AC.py:128-132): x in the box, x' equal to x except on the protected column (different value, inside
+    the box's range) and on the relaxed column (|difference| <= threshold), classes strictly different."""
+    name = "AC-3"
+    net = O.Net(*G.wb(name)); dom = G.domain(name)
+    pa, ra, thr = dom.columns.index("race"), dom.columns.index("age"), 5
+    c = next(iter(G.cases(name)))
+    rng = np.random.RandomState(3)
+    boxes = np.repeat(c["box"][None], 6, axis=0).copy()
+    boxes[:, 0, 0] = [10, 30, 50, 70, 90, 95]; boxes[:, 0, 1] = boxes[:, 0, 0] + 5
+    samples = rng.randint(boxes[:, None, :, 0], boxes[:, None, :, 1] + 1, size=(6, 40, dom.d)).astype(np.int32)
+    ce, vp, vn, dp, dn = O.partition_screen_ex(net, samples, boxes, pa, ra, thr)
+    strict = O.partition_screen(net, samples, boxes, pa)
+    found_relaxed_only = 0
+    for p in range(6):
+        lo, hi = boxes[p, pa]
+        first = -1
+        for s in range(40):
+            x = samples[p, s].astype(np.float32)
+            base = []
+            for v in range(lo, hi + 1):
+                xv = x.copy(); xv[pa] = v
+                base.append(O.forward_f32(net, xv[None])[0])
+            exists = False
+            for i, v in enumerate(range(lo, hi + 1)):
+                for v2 in range(lo, hi + 1):
+                    if v2 == v:
+                        continue
+                    for d in range(-thr, thr + 1):
+                        x2 = x.copy(); x2[pa] = v2; x2[ra] = x[ra] + d
+                        y2 = O.forward_f32(net, x2[None])[0]
+                        if (base[i] > 0 and y2 < 0) or (base[i] < 0 and y2 > 0):
+                            exists = True
+            if exists:
+                first = s
+                break
+        assert ce[p] == first, (p, ce[p], first)
+        if strict[0][p] >= 0 and strict[0][p] == ce[p]:
+            assert (vp[p], vn[p], dp[p], dn[p]) == (strict[1][p], strict[2][p], 0, 0)
+        if ce[p] >= 0:
+            x = samples[p, ce[p]].astype(np.float32)
+            xp = x.copy(); xp[pa] = vp[p]; xp[ra] += dp[p]
+            xn = x.copy(); xn[pa] = vn[p]; xn[ra] += dn[p]
+            assert O.forward_f32(net, xp[None])[0] > 0 > O.forward_f32(net, xn[None])[0]
+            assert vp[p] != vn[p] and (dp[p] == 0 or dn[p] == 0) and max(abs(dp[p]), abs(dn[p])) <= thr
+            found_relaxed_only += int(strict[0][p] != ce[p])
+    assert np.array_equal(O.partition_screen_ex(net, samples, boxes, pa, -1, 0)[0], strict[0])
+
+
+def test_no_preactivation_sign_depends_on_the_summation_order():
+    """On every fixture: the smallest |pre-activation| relative to the size of its terms is far above the rounding error a
+    different summation order (numpy's BLAS, the reference) could introduce, so the activation counts are order-proof."""
+    worst = 1.0
+    for name in MODELS:
+        net = O.Net(*G.wb(name))
+        for c in G.cases(name):
+            cnt, best = O.nearzero(net, c["samples"][None])
+            assert cnt == 0, (c["tag"], cnt, best)
+            worst = min(worst, best)
+    assert worst > 2.0 ** -40
