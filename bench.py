@@ -190,8 +190,14 @@ def run_gpu(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    saved_stdout = None
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # NCCL's version banner must not share stdout with the JSON line
+        # NCCL prints its version banner on stdout when the first communicator comes up; stdout must carry the one JSON
+        # line and nothing else, so file descriptor 1 points at stderr until that line is printed
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -530,6 +536,9 @@ def run_gpu(args):
                   "relaxed_targeted_ac_models_config_5": ac_sweep,
                   "bm_sweep_20000_partitions_S1000": bm_sweep},
     }
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -281,12 +281,15 @@ struct FbIbpMasks {
     }
 };
 
-template <class S, int l, int INW>
+// FMA0: the box is small enough (|x| < 2^29) that a float32-valued weight times an input of layer 0 has at most 53
+// significant bits.  The product is then exact, "round the product, then round the sum" equals one fused multiply-add in
+// every rounding mode, and layer 0 -- most of the weights of the small networks -- costs half the FP64 instructions.
+template <class S, int l, int INW, bool FMA0>
 __device__ __forceinline__ void fb_ibp_loop_layer(const SpecParams<S, double> &prm, const double (&lb)[INW], const double (&ub)[INW],
                                                   const double (&lbd)[INW], const double (&ubd)[INW], double *scol,
                                                   FbIbpMasks<S::NW> &mk, const uint32_t *cnt, const double *tol,
                                                   const uint32_t *unb, const FbPruneOut &o, int64_t p, double &out_lb_rd,
-                                                  double &out_ub_ru, bool exact0)
+                                                  double &out_ub_ru)
 {
     constexpr int IN = S::dim(l), OUT = S::dim(l + 1), BO = S::boff(l), N = S::N;
     constexpr bool last = (l == S::NL - 1), first = (l == 0);
@@ -305,18 +308,16 @@ __device__ __forceinline__ void fb_ibp_loop_layer(const SpecParams<S, double> &p
             const double w = wj[i * istride];
             const bool neg = fb_signbit(w);            // host canonicalises -0.0 to +0.0
             const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+            if (first && FMA0) {                       // exact products (see FMA0)
+                mn = __fma_rn(w, a, mn); mx = __fma_rn(w, b, mx);
+                mnd = __fma_rd(w, a, mnd); mxd = __fma_ru(w, b, mxd);
+                continue;
+            }
             mn = __dadd_rn(mn, __dmul_rn(w, a));
             mx = __dadd_rn(mx, __dmul_rn(w, b));
-            if (first) {
-                // integer inputs: both chains read the same box, and while |x| < 2^29 a float32-valued weight times x
-                // has at most 53 significant bits, so the product is exact and the three roundings of it coincide
-                if (exact0) {
-                    mnd = __dadd_rd(mnd, __dmul_rn(w, a));
-                    mxd = __dadd_ru(mxd, __dmul_rn(w, b));
-                } else {
-                    mnd = __dadd_rd(mnd, __dmul_rd(w, a));
-                    mxd = __dadd_ru(mxd, __dmul_ru(w, b));
-                }
+            if (first) {                               // integer inputs: both chains read the same box
+                mnd = __dadd_rd(mnd, __dmul_rd(w, a));
+                mxd = __dadd_ru(mxd, __dmul_ru(w, b));
             } else {
                 const double ad = neg ? ubd[i] : lbd[i], bd = neg ? lbd[i] : ubd[i];
                 mnd = __dadd_rd(mnd, __dmul_rd(w, ad));
@@ -387,7 +388,7 @@ __device__ __forceinline__ void fb_ibp_loop_layer(const SpecParams<S, double> &p
         FbIbpMasks<S::NW>::template put<BO>(mk.cand, cand64); FbIbpMasks<S::NW>::template put<BO>(mk.bdead, bdead64);
         FbIbpMasks<S::NW>::template put<BO>(mk.sliver, sliver64); FbIbpMasks<S::NW>::template put<BO>(mk.sdead, sdead64);
         FbIbpMasks<S::NW>::template put<BO>(mk.scand, scand64); FbIbpMasks<S::NW>::template put<BO>(mk.dead, dead64);
-        fb_ibp_loop_layer<S, l + 1, INW>(prm, nlb, nub, nlbd, nubd, scol, mk, cnt, tol, unb, o, p, out_lb_rd, out_ub_ru, exact0);
+        fb_ibp_loop_layer<S, l + 1, INW, FMA0>(prm, nlb, nub, nlbd, nubd, scol, mk, cnt, tol, unb, o, p, out_lb_rd, out_ub_ru);
     } else {
         // the single output neuron: candidate copied through, then cleared by the keep-one fix of its 1-element list
         FbIbpMasks<S::NW>::template put<BO>(mk.cand, cand64);
@@ -409,19 +410,24 @@ fb_ibp_loop_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
     for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
         double lb[INW], ub[INW];
         const int2 *bx = reinterpret_cast<const int2 *>(boxes + p * (2 * D0));
-        bool exact0 = true;
+        bool small = true;
 #pragma unroll
         for (int i = 0; i < D0; ++i) {
             const int2 b = __ldg(bx + i);
             lb[i] = (double)b.x; ub[i] = (double)b.y;
-            exact0 = exact0 && b.x > -(1 << 29) && b.x < (1 << 29) && b.y > -(1 << 29) && b.y < (1 << 29);
+            small = small && b.x > -(1 << 29) && b.x < (1 << 29) && b.y > -(1 << 29) && b.y < (1 << 29);
         }
         FbIbpMasks<NW> mk;
 #pragma unroll
         for (int k = 0; k < NW; ++k) { mk.cand[k] = 0; mk.bdead[k] = 0; mk.sliver[k] = 0; mk.sdead[k] = 0; mk.scand[k] = 0; mk.dead[k] = 0; }
         double out_lb_rd = 0.0, out_ub_ru = 0.0;
-        fb_ibp_loop_layer<S, 0, INW>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
-                                     out_lb_rd, out_ub_ru, exact0);
+        // (two copies of the network's code, chosen by a real branch: ptxas does not if-convert across the neuron loops)
+        if (small)
+            fb_ibp_loop_layer<S, 0, INW, true>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
+                                               out_lb_rd, out_ub_ru);
+        else
+            fb_ibp_loop_layer<S, 0, INW, false>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
+                                                out_lb_rd, out_ub_ru);
         uint32_t anysl = 0;
 #pragma unroll
         for (int k = 0; k < NW; ++k) {

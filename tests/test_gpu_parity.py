@@ -128,6 +128,27 @@ def test_singular_verification_matches_reference_z3(eng, name):
         assert hits > 0 and r.bits("s_dead").sum() == hits
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-11", "GC-4", "GC-1"])
+def test_bounds_on_boxes_beyond_the_exact_product_range(eng, name):
+    """The looped bounds kernel fuses product and sum in layer 0 only while |x| < 2^29 keeps the products exact; boxes
+    beyond that take its unfused path.  Both must give the oracle's bounds bit for bit, mixed in one batch."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    base = np.array([[dom.ranges[c][0], dom.ranges[c][1]] for c in dom.columns], dtype=np.int32)
+    boxes = np.repeat(base[None], 6, axis=0).copy()
+    boxes[1, 0] = [-(2 ** 29) - 5, 2 ** 29 + 7]
+    boxes[2, 2] = [2 ** 30, 2 ** 31 - 1]
+    boxes[3, 1] = [-(2 ** 31), -(2 ** 30)]
+    boxes[4, 0] = [2 ** 29 - 1, 2 ** 29 - 1]
+    boxes[5, 0] = [2 ** 29, 2 ** 29]
+    r = m.ibp(boxes, want=eng.BOUND_OUTPUTS + ("b_dead", "verdict"))
+    o_rn = O.ibp(net, boxes); o_dir = O.ibp_directed(net, boxes)
+    for key, ref in zip(("ws_lb", "ws_ub", "pl_lb", "pl_ub"), o_rn):
+        assert np.array_equal(r.numpy(key), ref), key
+    assert np.array_equal(r.numpy("lb_rd"), o_dir[0]) and np.array_equal(r.numpy("ub_ru"), o_dir[1])
+
+
 def test_sliver_flag_set_by_a_constructed_case(eng):
     """A network built so that the singular-verification quantity of a hidden neuron lands inside the tolerance: the
     device must flag it (sliver bit + FB_VERDICT_SLIVER), exactly like the oracle, on layer 0 (quantity = ws_ub) and

@@ -9,8 +9,25 @@ from fairify_b200 import engine
 _models = {}
 
 
+_by_id = collections.OrderedDict()
+
+
 def model_for(w, b):
-    """engine.Model for these weights (cached by content: the drivers pass freshly pruned arrays each time)."""
+    """engine.Model for these weights (cached by content: the drivers pass freshly pruned arrays each time; and by
+    identity of the arrays, which are kept alive while cached, so that the partition loop's repeated calls with the
+    same lists do not re-hash the weights)."""
+    ident = tuple(id(a) for a in w) + tuple(id(a) for a in b)
+    hit = _by_id.get(ident)
+    if hit is not None:
+        return hit[0]
+    m = _model_by_content(w, b)
+    _by_id[ident] = (m, list(w), list(b))
+    while len(_by_id) > 16:
+        _by_id.popitem(last=False)
+    return m
+
+
+def _model_by_content(w, b):
     h = hashlib.blake2b(digest_size=16)
     for a in list(w) + list(b):
         a = np.ascontiguousarray(a, dtype=np.float32)

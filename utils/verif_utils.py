@@ -45,7 +45,12 @@ def get_y_pred(net, w, b, X_test):
     if not _is_device_net(net):            # a foreign `net`: honour it, row by row, like the reference
         return [np.asarray(sigmoid(net(x, w, b))) > 0.5 for x in X]
     y = _device.logits(X, w, b)
-    return [np.array([sigmoid(v) > 0.5]) for v in y]
+    # sigmoid(v) > 0.5 is v > 0 except within 1e-10 of zero, where exp(-v) rounds to 1 and the reference's formula
+    # answers False for tiny positive logits: those few go through the formula itself
+    flags = np.asarray(y) > 0
+    for k in np.flatnonzero(np.abs(y) < 1e-10):
+        flags[k] = sigmoid(float(y[k])) > 0.5
+    return list(flags.reshape(-1, 1))            # 1-element bool arrays, like the reference's list
 
 
 def y_pred_mismatch(net, w, b, pr_w, pr_b, X_test, y_test):
