@@ -264,7 +264,12 @@ template <class S> __host__ __device__ constexpr int fb_ibp_max_hidden()
     for (int l = 1; l < S::NL; ++l) r = S::dim(l) > r ? S::dim(l) : r;      // inputs of layers 1 .. (hidden widths)
     return r;
 }
-template <class S> __host__ __device__ constexpr bool fb_ibp_loop_ok() { return fb_ibp_max_hidden<S>() <= FB_IBP_LOOP_MAXW && S::NL >= 2; }
+// networks with ONE hidden layer (any width up to 128) take the fused form below: no hidden bounds are stored at all
+template <class S> __host__ __device__ constexpr bool fb_ibp_fused2_ok() { return S::NL == 2 && S::dim(1) <= 128; }
+template <class S> __host__ __device__ constexpr bool fb_ibp_loop_ok()
+{
+    return fb_ibp_fused2_ok<S>() || (fb_ibp_max_hidden<S>() <= FB_IBP_LOOP_MAXW && S::NL >= 2);
+}
 
 template <int NW>
 struct FbIbpMasks {
@@ -396,6 +401,97 @@ __device__ __forceinline__ void fb_ibp_loop_layer(const SpecParams<S, double> &p
     }
 }
 
+// One hidden layer (d - H - 1): every finished hidden neuron is folded straight into the four accumulators of the
+// logit (terms in ascending neuron order, separately rounded product and sum -- the order and the arithmetic of
+// neuron_bounds), so the hidden layer's bounds never sit anywhere: live state is the box and four doubles.  Neurons
+// [64 * HALF, 64 * HALF + 64) of the hidden layer; returns whether all of them ended up in b_dead (keep-one fix).
+template <class S, bool FMA0, int HALF>
+__device__ __forceinline__ bool fb_ibp_fused2_half(const SpecParams<S, double> &prm, const double (&lb)[S::D0], const double (&ub)[S::D0],
+                                                   FbIbpMasks<S::NW> &mk, const uint32_t *cnt, const double *tol, const FbPruneOut &o,
+                                                   int64_t p, double &omn, double &omx, double &omnd, double &omxd)
+{
+    constexpr int IN = S::D0, H = S::dim(1), N = S::N;
+    constexpr int J0 = 64 * HALF, J1 = (H < J0 + 64) ? H : J0 + 64, CNT = J1 - J0;
+    constexpr uint64_t full = CNT == 64 ? ~0ull : ((1ull << CNT) - 1ull);
+    uint64_t cand64 = 0, bdead64 = 0, bcand64 = 0, sliver64 = 0;
+    const double *w0 = prm.w + S::woff(0);              // layer 0 is stored [out][in]
+    const double *w1 = prm.w + S::woff(1);              // layer 1 [in][out] with out = 1
+#pragma unroll 1
+    for (int j = J0; j < J1; ++j) {
+        const double *wj = w0 + j * IN;
+        double mn = 0.0, mx = 0.0, mnd = 0.0, mxd = 0.0;
+#pragma unroll
+        for (int i = 0; i < IN; ++i) {
+            const double w = wj[i];
+            const bool neg = fb_signbit(w);
+            const double a = neg ? ub[i] : lb[i], b = neg ? lb[i] : ub[i];
+            if (FMA0) {
+                mn = __fma_rn(w, a, mn); mx = __fma_rn(w, b, mx); mnd = __fma_rd(w, a, mnd); mxd = __fma_ru(w, b, mxd);
+            } else {
+                mn = __dadd_rn(mn, __dmul_rn(w, a)); mx = __dadd_rn(mx, __dmul_rn(w, b));
+                mnd = __dadd_rd(mnd, __dmul_rd(w, a)); mxd = __dadd_ru(mxd, __dmul_ru(w, b));
+            }
+        }
+        const double bj = prm.b[j];
+        const double wlo = __dadd_rn(mn, bj), wup = __dadd_rn(mx, bj), wld = __dadd_rd(mnd, bj), wud = __dadd_ru(mxd, bj);
+        const uint32_t c32 = cnt ? cnt[j] : 0u;
+        const bool c = c32 == 0, le0 = wup <= 0.0;
+        const uint64_t bit = 1ull << (j - J0);
+        if (c) cand64 |= bit;
+        if (c && le0) bdead64 |= bit;
+        if (c && !le0) bcand64 |= bit;
+        if (tol != nullptr && c && !le0 && wup <= tol[j]) sliver64 |= bit;
+        const double plb = wlo < 0.0 ? 0.0 : wlo, pub = wup < 0.0 ? 0.0 : wup;
+        const double plbd = wld < 0.0 ? 0.0 : wld, pubd = wud < 0.0 ? 0.0 : wud;
+        if (o.counts16) o.counts16[p * N + j] = (uint16_t)c32;
+        if (o.ws_lb) o.ws_lb[p * N + j] = wlo;
+        if (o.ws_ub) o.ws_ub[p * N + j] = wup;
+        if (o.pl_lb) o.pl_lb[p * N + j] = plb;
+        if (o.pl_ub) o.pl_ub[p * N + j] = pub;
+        if (o.lb_rd) o.lb_rd[p * N + j] = wld;
+        if (o.ub_ru) o.ub_ru[p * N + j] = wud;
+        const double v = w1[j];
+        const bool vneg = fb_signbit(v);
+        omn = __dadd_rn(omn, __dmul_rn(v, vneg ? pub : plb));
+        omx = __dadd_rn(omx, __dmul_rn(v, vneg ? plb : pub));
+        omnd = __dadd_rd(omnd, __dmul_rd(v, vneg ? pubd : plbd));
+        omxd = __dadd_ru(omxd, __dmul_ru(v, vneg ? plbd : pubd));
+    }
+    FbIbpMasks<S::NW>::template put<J0>(mk.cand, cand64); FbIbpMasks<S::NW>::template put<J0>(mk.bdead, bdead64);
+    FbIbpMasks<S::NW>::template put<J0>(mk.sliver, sliver64); FbIbpMasks<S::NW>::template put<J0>(mk.scand, bcand64);
+    return bdead64 == full;
+}
+
+template <class S, bool FMA0>
+__device__ __forceinline__ void fb_ibp_fused2(const SpecParams<S, double> &prm, const double (&lb)[S::D0], const double (&ub)[S::D0],
+                                              FbIbpMasks<S::NW> &mk, const uint32_t *cnt, const double *tol, const FbPruneOut &o,
+                                              int64_t p, double &out_lb_rd, double &out_ub_ru)
+{
+    constexpr int H = S::dim(1), N = S::N, NW = S::NW;
+    double omn = 0.0, omx = 0.0, omnd = 0.0, omxd = 0.0;
+    bool all = fb_ibp_fused2_half<S, FMA0, 0>(prm, lb, ub, mk, cnt, tol, o, p, omn, omx, omnd, omxd);
+    if constexpr (H > 64) all = fb_ibp_fused2_half<S, FMA0, 1>(prm, lb, ub, mk, cnt, tol, o, p, omn, omx, omnd, omxd) && all;
+    if (all) mk.bdead[0] &= ~1u;                                  // keep-one fix of the hidden layer (bit 0 = neuron 0)
+#pragma unroll
+    for (int k = 0; k < NW; ++k) mk.dead[k] = mk.bdead[k];       // s_dead is empty on layer 0 (its query's quantity is ws_ub > 0)
+    // the logit
+    const double bo = prm.b[H];
+    const double wlo = __dadd_rn(omn, bo), wup = __dadd_rn(omx, bo), wld = __dadd_rd(omnd, bo), wud = __dadd_ru(omxd, bo);
+    const uint32_t c32 = cnt ? cnt[H] : 0u;
+    if (c32 == 0) {                                               // candidate copied through; keep-one clears its dead bits
+        mk.cand[H >> 5] |= 1u << (H & 31);
+        mk.scand[H >> 5] |= 1u << (H & 31);
+    }
+    out_lb_rd = wld; out_ub_ru = wud;
+    if (o.counts16) o.counts16[p * N + H] = (uint16_t)c32;
+    if (o.ws_lb) o.ws_lb[p * N + H] = wlo;
+    if (o.ws_ub) o.ws_ub[p * N + H] = wup;
+    if (o.pl_lb) o.pl_lb[p * N + H] = wlo < 0.0 ? 0.0 : wlo;
+    if (o.pl_ub) o.pl_ub[p * N + H] = wup < 0.0 ? 0.0 : wup;
+    if (o.lb_rd) o.lb_rd[p * N + H] = wld;
+    if (o.ub_ru) o.ub_ru[p * N + H] = wud;
+}
+
 template <class S>
 __global__ void __launch_bounds__(FB_IBP_LOOP_THREADS)
 fb_ibp_loop_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n, const int32_t *__restrict__ boxes,
@@ -403,7 +499,8 @@ fb_ibp_loop_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
                    const uint32_t *__restrict__ unb, const __grid_constant__ FbPruneOut out)
 {
     constexpr int D0 = S::D0, NW = S::NW, N = S::N;
-    constexpr int INW = fb_ibp_max_hidden<S>() > D0 ? fb_ibp_max_hidden<S>() : D0;
+    constexpr bool FUSED2 = fb_ibp_fused2_ok<S>();
+    constexpr int INW = (FUSED2 || fb_ibp_max_hidden<S>() <= D0) ? D0 : fb_ibp_max_hidden<S>();
     extern __shared__ __align__(16) unsigned char fb_smem[];                 // [max hidden width][4][threads] doubles
     double *scol = reinterpret_cast<double *>(fb_smem) + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -422,12 +519,17 @@ fb_ibp_loop_kernel(const __grid_constant__ SpecParams<S, double> prm, int64_t n,
         for (int k = 0; k < NW; ++k) { mk.cand[k] = 0; mk.bdead[k] = 0; mk.sliver[k] = 0; mk.sdead[k] = 0; mk.scand[k] = 0; mk.dead[k] = 0; }
         double out_lb_rd = 0.0, out_ub_ru = 0.0;
         // (two copies of the network's code, chosen by a real branch: ptxas does not if-convert across the neuron loops)
-        if (small)
-            fb_ibp_loop_layer<S, 0, INW, true>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
-                                               out_lb_rd, out_ub_ru);
-        else
-            fb_ibp_loop_layer<S, 0, INW, false>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
-                                                out_lb_rd, out_ub_ru);
+        if constexpr (FUSED2) {
+            if (small) fb_ibp_fused2<S, true>(prm, lb, ub, mk, counts ? counts + p * N : nullptr, tol, out, p, out_lb_rd, out_ub_ru);
+            else fb_ibp_fused2<S, false>(prm, lb, ub, mk, counts ? counts + p * N : nullptr, tol, out, p, out_lb_rd, out_ub_ru);
+        } else {
+            if (small)
+                fb_ibp_loop_layer<S, 0, INW, true>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
+                                                   out_lb_rd, out_ub_ru);
+            else
+                fb_ibp_loop_layer<S, 0, INW, false>(prm, lb, ub, lb, ub, scol, mk, counts ? counts + p * N : nullptr, tol, unb, out, p,
+                                                    out_lb_rd, out_ub_ru);
+        }
         uint32_t anysl = 0;
 #pragma unroll
         for (int k = 0; k < NW; ++k) {

@@ -19,7 +19,7 @@ typedef cudaError_t (*FbIbpLaunch)(const void *p64, int64_t n, const int32_t *bo
                                    const double *tol, const uint32_t *unb, const FbPruneOut *out, int num_sms,
                                    cudaStream_t st);
 
-template <class S, bool BUILD = (S::P <= FB_IBP_SPEC_MAX_WEIGHTS)>
+template <class S, bool BUILD = (S::P <= FB_IBP_SPEC_MAX_WEIGHTS || fb_ibp_fused2_ok<S>())>
 struct FbSpecIbpOps {
     using P64 = SpecParams<S, double>;
     static cudaError_t ibp(const void *p64, int64_t n, const int32_t *boxes, const uint32_t *counts, const double *tol,
@@ -29,9 +29,9 @@ struct FbSpecIbpOps {
         // FAIRIFY_B200_IBP_UNROLLED=1 keeps the fully unrolled kernel for the shapes the looped one covers (comparisons)
         static const bool unrolled = [] { const char *v = getenv("FAIRIFY_B200_IBP_UNROLLED"); return v && v[0] == '1'; }();
         if constexpr (fb_ibp_loop_ok<S>()) {
-            if (!unrolled) {
+            if (!unrolled || S::P > FB_IBP_SPEC_MAX_WEIGHTS) {
                 auto k = fb_ibp_loop_kernel<S>;
-                const size_t smem = sizeof(double) * 4 * FB_IBP_LOOP_THREADS * fb_ibp_max_hidden<S>();
+                const size_t smem = fb_ibp_fused2_ok<S>() ? 0 : sizeof(double) * 4 * FB_IBP_LOOP_THREADS * fb_ibp_max_hidden<S>();
                 cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
                 if (e != cudaSuccess) return e;
                 const int64_t ctas = (n + FB_IBP_LOOP_THREADS - 1) / FB_IBP_LOOP_THREADS;
@@ -40,10 +40,14 @@ struct FbSpecIbpOps {
                 return cudaGetLastError();
             }
         }
-        auto k = fb_ibp_spec_kernel<S>;
-        const int64_t ctas = (n + FB_IBP_THREADS - 1) / FB_IBP_THREADS;
-        k<<<fb_grid_for(k, FB_IBP_THREADS, 0, ctas, num_sms), FB_IBP_THREADS, 0, st>>>(prm, n, boxes, counts, tol, unb, *out);
-        return cudaGetLastError();
+        if constexpr (S::P <= FB_IBP_SPEC_MAX_WEIGHTS) {
+            auto k = fb_ibp_spec_kernel<S>;
+            const int64_t ctas = (n + FB_IBP_THREADS - 1) / FB_IBP_THREADS;
+            k<<<fb_grid_for(k, FB_IBP_THREADS, 0, ctas, num_sms), FB_IBP_THREADS, 0, st>>>(prm, n, boxes, counts, tol, unb, *out);
+            return cudaGetLastError();
+        } else {
+            return cudaErrorNotSupported;          // (no unrolled kernel is built for shapes this large)
+        }
     }
 
     static constexpr FbIbpLaunch launcher = &FbSpecIbpOps::ibp;
