@@ -403,7 +403,7 @@ def run_gpu(args):
             t0 = time.perf_counter()
             p_list = partitioned_ranges(rd.keys(), Dm.pa, partition(rd, Dm.threshold), rd)
             t_grid = time.perf_counter() - t0
-            count = min(len(p_list), 2000)
+            count = min(len(p_list), 4096)              # one full batching window
             np.random.seed(1)
             with contextlib.redirect_stdout(io.StringIO()):
                 t0 = time.perf_counter()

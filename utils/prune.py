@@ -257,9 +257,24 @@ def _compute(m, cols, boxes, S):
     return sims, states, arrays
 
 
+_xdf_cache = {}
+
+
+def _feature_frame(df, label_name):
+    """df without its label column (the reference drops it on every call, utils/prune.py:674; the drivers pass the
+    same frame for every partition, so the result is kept while the frame's column index object is the same)."""
+    hit = _xdf_cache.get(id(df))
+    if hit is not None and hit[0] is df.columns and hit[1] == label_name:
+        return hit[2]
+    x_df = df.drop(labels=[label_name], axis=1, inplace=False)
+    _xdf_cache.clear()
+    _xdf_cache[id(df)] = (df.columns, label_name, x_df, df)       # (df kept alive: its id cannot be reused)
+    return x_df
+
+
 def _sound_prune(label_name, df, weight, bias, simulation_size, layer_net, range_dict):
     global _window
-    x_df = df.drop(labels=[label_name], axis=1, inplace=False)
+    x_df = _feature_frame(df, label_name)
     cols = x_df.columns.values
     m = _device.model_for(weight, bias)
     S = int(simulation_size)
