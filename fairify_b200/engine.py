@@ -30,7 +30,13 @@ ALL_OUTPUTS = DEFAULT_OUTPUTS + BOUND_OUTPUTS + ("s_dead", "s_cand", "record")
 VERDICT_CERTIFIED, VERDICT_CE, VERDICT_SLIVER = 1, 2, 4
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream():
+    """torch's current stream on the current device, as the C-ABI's cudaStream_t."""
+    if _raw_stream is not None:                      # same value as below, without building a Stream object per call
+        return C.c_void_p(_raw_stream(torch.cuda.current_device()))
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
