@@ -30,6 +30,8 @@ def main():
     z = np.load(os.path.join(os.path.dirname(__file__), "..", "tests", "golden", "weights.npz"))
     peak = max(engine.fp64_peak(4096)[0] for _ in range(3))
     names = [f"AC-{k}" for k in range(1, 13)] + [f"GC-{k}" for k in range(1, 6)] + [f"BM-{k}" for k in range(1, 9)]
+    if len(sys.argv) > 1:
+        names = sys.argv[1:]
     print(f"B200, measured DFMA peak {peak:.2f} TFLOP/s; profile = 1000 Philox samples per partition\n")
     print("| model | layers | weights | profile kernel | partitions | profile evals/s | % of FP64 peak | bounds evals/s | bounds FP64 ops/s |")
     print("|---|---|---|---|---|---|---|---|---|")
