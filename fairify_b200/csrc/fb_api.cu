@@ -566,34 +566,35 @@ static int fb_profile_tiled(const fb_model *m, int64_t n, const int32_t *boxes, 
 
 template <int TM>
 static int fb_screen_tiled_launch(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
-                                  uint64_t seed, int64_t first_index, int pa_col, unsigned long long *key, cudaStream_t st)
+                                  uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_thr,
+                                  unsigned long long *key, cudaStream_t st)
 {
     const size_t smem = fb_screen_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, TM);
     if (samples == nullptr) {
         auto k = fb_screen_tile_kernel<TM, true>;
         FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k<<<fb_grid_for(k, FB_TILE_THREADS, smem, n, m->num_sms), FB_TILE_THREADS, smem, st>>>(
-            m->tile, n, boxes, samples, seed, first_index, S, pa_col, key);
+            m->tile, n, boxes, samples, seed, first_index, S, pa_col, ra_col, ra_thr, key);
     } else {
         auto k = fb_screen_tile_kernel<TM, false>;
         FB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k<<<fb_grid_for(k, FB_TILE_THREADS, smem, n, m->num_sms), FB_TILE_THREADS, smem, st>>>(
-            m->tile, n, boxes, samples, seed, first_index, S, pa_col, key);
+            m->tile, n, boxes, samples, seed, first_index, S, pa_col, ra_col, ra_thr, key);
     }
     FB_CUDA(cudaGetLastError());
     return FB_OK;
 }
 
 static int fb_screen_tiled(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S, uint64_t seed,
-                           int64_t first_index, int pa_col, unsigned long long *key, cudaStream_t st)
+                           int64_t first_index, int pa_col, int ra_col, int ra_thr, unsigned long long *key, cudaStream_t st)
 {
     // 128-row tiles where two CTAs of that size still share an SM (networks up to 64 wide: BM-7 38 vs 52 ms per 10^5
     // partitions), 64-row tiles otherwise (BM-4 42 vs 48 ms per 2*10^4, AC-4 90 vs 109 ms per 10^5 with 128)
     static const int forced_tm = [] { const char *v = getenv("FAIRIFY_B200_SCREEN_TM"); return v ? atoi(v) : 0; }();   // tuning aid
     const size_t smem128 = fb_screen_tile_smem_bytes(m->tile.maxw, (m->tile.maxw + 31) & ~31, 128);
     if (forced_tm != 64 && (smem128 <= 100 * 1024 || (forced_tm == 128 && smem128 <= 220 * 1024)))
-        return fb_screen_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, pa_col, key, st);
-    return fb_screen_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, pa_col, key, st);
+        return fb_screen_tiled_launch<128>(m, n, boxes, samples, S, seed, first_index, pa_col, ra_col, ra_thr, key, st);
+    return fb_screen_tiled_launch<64>(m, n, boxes, samples, S, seed, first_index, pa_col, ra_col, ra_thr, key, st);
 }
 
 static size_t fb_profile_gen_smem(const fb_model *m)
@@ -940,9 +941,9 @@ extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_
     if (fb_use_spec(m)) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));
-    } else if (fb_use_tiled_profile(m) && ra_col < 0) {
-        // (the tiled float32 screen of the big runtime-shape networks sweeps the protected column only)
-        if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, (unsigned long long *)key.p, st)) return rc;
+    } else if (fb_use_tiled_profile(m)) {
+        if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, ra_col, ra_threshold,
+                                     (unsigned long long *)key.p, st)) return rc;
     } else {
         const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
         if (samples == nullptr) {

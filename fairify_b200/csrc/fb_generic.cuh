@@ -413,11 +413,49 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
     return buf0 + (net.L & 1) * bufsz;
 }
 
+// One sample's sweep, row by row in the order fb_screen_sample evaluates it: rows 0 .. W-1 are the strict sweep of the
+// protected column (RA offset 0), then, in relaxed mode, W rows per RA offset d = -thr .. thr without 0.  row() is fed
+// the logits in that order and ends with the same key fb_screen_sample returns; `done` says no later row matters.
+struct FbScreenScan {
+    int vp, vp2, vn, vn2;                    // first / second protected offset with a positive / negative logit, -1 = none
+    uint32_t low;                            // 0xffffffff: no counterexample (yet)
+    bool done;
+    __device__ __forceinline__ void begin() { vp = vp2 = vn = vn2 = -1; low = 0xffffffffu; done = false; }
+    __device__ __forceinline__ void row(int q, float y, int W, bool relaxed, int thr)
+    {
+        if (done) return;
+        const int k = q / W, off = q - k * W;
+        if (k == 0) {
+            if (y > 0.0f) { if (vp < 0) vp = off; else if (vp2 < 0) vp2 = off; }
+            if (y < 0.0f) { if (vn < 0) vn = off; else if (vn2 < 0) vn2 = off; }
+            if (off == W - 1) {
+                if (vp >= 0 && vn >= 0) {
+                    low = relaxed ? ((uint32_t)vp << 24) | ((uint32_t)vn << 16) | (128u << 8) | 128u
+                                  : ((uint32_t)vp << 16) | (uint32_t)vn;
+                    done = true;
+                } else if (!relaxed || (vp < 0) == (vn < 0)) {
+                    done = true;                                        // one sweep only, or no class at all
+                }
+            }
+            return;
+        }
+        int d = -thr + (k - 1);
+        if (d >= 0) ++d;
+        if (vp >= 0 && y < 0.0f) {
+            const int partner = (vp != off) ? vp : vp2;
+            if (partner >= 0) { low = ((uint32_t)partner << 24) | ((uint32_t)off << 16) | (128u << 8) | (uint32_t)(d + 128); done = true; }
+        } else if (vn >= 0 && y > 0.0f) {
+            const int partner = (vn != off) ? vn : vn2;
+            if (partner >= 0) { low = ((uint32_t)off << 24) | ((uint32_t)partner << 16) | ((uint32_t)(d + 128) << 8) | 128u; done = true; }
+        }
+    }
+};
+
 template <int TM, bool PHILOX>
 __global__ void __launch_bounds__(FB_TILE_THREADS)
 fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict__ boxes,
                       const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp, int pa_col,
-                      unsigned long long *__restrict__ ce_key)
+                      int ra_col, int ra_thr, unsigned long long *__restrict__ ce_key)
 {
     extern __shared__ __align__(16) unsigned char fb_smem[];
     float *buf0 = reinterpret_cast<float *>(fb_smem);
@@ -425,24 +463,27 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
     const int maxwp = (net.maxw + 31) & ~31;
     float *wst = buf0 + 2 * (size_t)bufsz;
     unsigned long long *s_best = reinterpret_cast<unsigned long long *>(wst + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp);
-    int *s_state = reinterpret_cast<int *>(s_best + 1);                 // havep, vp, haven, vn of a segmented sweep
+    int *s_state = reinterpret_cast<int *>(s_best + 1);                 // "this sample's sweep is decided" of a segmented sweep
     const int tid = threadIdx.x;
     const int D0 = net.dims[0];
+    const bool relaxed = ra_col >= 0;
+    const int nd = relaxed ? 2 * ra_thr + 1 : 1;                        // RA offsets per protected value
     for (int64_t p = blockIdx.x; p < n; p += gridDim.x) {
         const int32_t *box = boxes + p * (2 * D0);
         const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
         const uint32_t Wu = (uint32_t)(pa_hi - pa_lo + 1);
-        if (Wu == 0 || Wu > FB_SCREEN_MAX_W_STRICT) {                      // does not fit the key's 16-bit fields
+        if (Wu == 0 || Wu > (relaxed ? FB_SCREEN_MAX_W_RELAXED : FB_SCREEN_MAX_W_STRICT)) {   // does not fit the key's fields
             if (tid == 0) ce_key[p] = FB_SCREEN_SKIPPED;
             continue;
         }
         const int W = (int)Wu;
+        const int R = W * nd;                                            // rows of one sample's sweep
         const int grp = PHILOX ? fb_draw_group(fb_box_widest(box, D0)) : 1;
         const int64_t pidx = first_index + p;
         if (tid == 0) *s_best = ~0ull;
         __syncthreads();
-        // row t of a tile: sample s_row, protected value v_row (or a zero row past the end)
-        auto fill = [&](int s_row, int v_row, bool exists) {
+        // row t of a tile: sample s_row, row q of its sweep (or a zero row past the end)
+        auto fill = [&](int s_row, int q, bool exists) {
             float *col = buf0 + tid;
             if (exists) {
                 if (PHILOX) fb_draw_row<float>(box, D0, grp, (uint32_t)s_row, pidx, seed, col, TM);
@@ -450,53 +491,54 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
                     const int32_t *row = samples + ((int64_t)p * nsamp + s_row) * D0;
                     for (int i = 0; i < D0; ++i) col[(size_t)i * TM] = (float)__ldg(row + i);
                 }
-                col[(size_t)pa_col * TM] = (float)v_row;
+                const int k = q / W, off = q - k * W;
+                col[(size_t)pa_col * TM] = (float)(pa_lo + off);
+                if (relaxed) {
+                    int d = k == 0 ? 0 : -ra_thr + (k - 1);
+                    if (k != 0 && d >= 0) ++d;
+                    col[(size_t)ra_col * TM] = (float)((int)col[(size_t)ra_col * TM] + d);
+                }
             } else {
                 for (int i = 0; i < D0; ++i) col[(size_t)i * TM] = 0.0f;
             }
         };
-        if (W <= TM) {
-            const int spt = TM / W;                                       // whole samples per tile
+        if (R <= TM) {
+            const int spt = TM / R;                                       // whole samples per tile
             for (int sbase = 0; sbase < nsamp; sbase += spt) {
                 const int ns = min(spt, nsamp - sbase);
-                if (tid < TM) fill(sbase + tid / W, pa_lo + tid % W, tid < ns * W);
+                if (tid < TM) fill(sbase + tid / R, tid % R, tid < ns * R);
                 __syncthreads();
                 const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
                 if (tid < ns) {
-                    bool havep = false, haven = false;
-                    int vp = 0, vn = 0;
-                    for (int vi = 0; vi < W; ++vi) {
-                        const float yv = y[tid * W + vi];
-                        if (yv > 0.0f && !havep) { havep = true; vp = vi; }
-                        if (yv < 0.0f && !haven) { haven = true; vn = vi; }
-                    }
-                    if (havep && haven)
-                        atomicMin(s_best, ((unsigned long long)(uint32_t)(sbase + tid) << 32) |
-                                              ((unsigned long long)(uint32_t)vp << 16) | (unsigned long long)(uint32_t)vn);
+                    FbScreenScan sc;
+                    sc.begin();
+                    for (int q = 0; q < R && !sc.done; ++q) sc.row(q, y[tid * R + q], W, relaxed, ra_thr);
+                    if (sc.low != 0xffffffffu)
+                        atomicMin(s_best, ((unsigned long long)(uint32_t)(sbase + tid) << 32) | (unsigned long long)sc.low);
                 }
                 __syncthreads();
                 if (*s_best != ~0ull) break;
             }
         } else {
+            FbScreenScan sc;                                              // thread 0's, carried across the segments
             for (int s = 0; s < nsamp; ++s) {
-                if (tid == 0) { s_state[0] = 0; s_state[1] = 0; s_state[2] = 0; s_state[3] = 0; }
-                for (int v0 = 0; v0 < W; v0 += TM) {
-                    const int nv = min(TM, W - v0);
-                    if (tid < TM) fill(s, pa_lo + v0 + tid, tid < nv);
+                sc.begin();
+                if (tid == 0) s_state[0] = 0;
+                for (int q0 = 0; q0 < R; q0 += TM) {
+                    const int nq = min(TM, R - q0);
+                    if (tid < TM) fill(s, q0 + tid, tid < nq);
                     __syncthreads();
                     const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
                     if (tid == 0) {
-                        for (int vi = 0; vi < nv; ++vi) {
-                            const float yv = y[vi];
-                            if (yv > 0.0f && !s_state[0]) { s_state[0] = 1; s_state[1] = v0 + vi; }
-                            if (yv < 0.0f && !s_state[2]) { s_state[2] = 1; s_state[3] = v0 + vi; }
+                        for (int t = 0; t < nq && !sc.done; ++t) sc.row(q0 + t, y[t], W, relaxed, ra_thr);
+                        if (sc.done) {
+                            s_state[0] = 1;
+                            if (sc.low != 0xffffffffu) *s_best = ((unsigned long long)(uint32_t)s << 32) | (unsigned long long)sc.low;
                         }
                     }
                     __syncthreads();
+                    if (s_state[0]) break;
                 }
-                if (tid == 0 && s_state[0] && s_state[2])
-                    *s_best = ((unsigned long long)(uint32_t)s << 32) | ((unsigned long long)(uint32_t)s_state[1] << 16) |
-                              (unsigned long long)(uint32_t)s_state[3];
                 __syncthreads();
                 if (*s_best != ~0ull) break;
             }

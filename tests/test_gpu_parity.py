@@ -470,6 +470,26 @@ def test_relaxed_partition_screen_matches_oracle(eng, name):
     assert (ce >= 0).sum() >= (strict[0].cpu().numpy() >= 0).sum()
 
 
+@pytest.mark.parametrize("name,thr", [("AC-5", 20), ("AC-4", 13), ("AC-1", 20)])
+def test_relaxed_screen_with_a_sweep_wider_than_a_tile(eng, name, thr):
+    """A relaxed sweep of W * (2 thr + 1) rows per sample that does not fit one tile of the big networks' screen kernel
+    (cut into segments, decided row by row in the oracle's order): same answers as the oracle."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    pa, ra = dom.columns.index("race"), dom.columns.index("age")
+    grid = eng.Grid(dom.columns, dom.ranges, 6)
+    first, n, S = len(grid) // 5, 14, 9
+    boxes = grid.boxes(first, n); hb = boxes.cpu().numpy()
+    samples = O.philox_samples(5, first, hb, S)
+    want = O.partition_screen_ex(net, samples, hb, pa, ra, thr)
+    got = m.partition_screen(boxes, pa, S=S, seed=5, first_index=first, ra_col=ra, ra_threshold=thr)
+    for g_, w_, key in zip(got, want, ("ce_sample", "pa_pos", "pa_neg", "ra_dpos", "ra_dneg")):
+        assert np.array_equal(g_.cpu().numpy(), w_), key
+    got2 = m.partition_screen(boxes, pa, samples=samples, ra_col=ra, ra_threshold=thr)
+    assert all(np.array_equal(a.cpu().numpy(), b_) for a, b_ in zip(got2, want))
+
+
 def test_partition_screen_rejects_what_it_cannot_encode(eng):
     """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
     w, b = G.wb("GC-1")
