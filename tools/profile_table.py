@@ -19,11 +19,15 @@ MMA_SPEC = {(13, 100, 100, 1), (13, 64, 64, 1), (16, 150, 100, 50, 1), (16, 64, 
             (13, 64, 32, 16, 8, 4, 1), (16, 64, 32, 16, 8, 4, 1), (20, 64, 32, 16, 8, 4, 1)}      # fb_spec_lists.h
 
 
-def timed(fn, reps=3):
-    for _ in range(reps):
+def timed(fn, reps=5):
+    """median of `reps` timed calls after one warm-up call (the first call of a kernel also pays its module load)"""
+    ts = []
+    for k in range(reps + 1):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); fn(); b.record(); torch.cuda.synchronize()
-    return a.elapsed_time(b)
+        if k:
+            ts.append(a.elapsed_time(b))
+    return sorted(ts)[len(ts) // 2]
 
 
 def main():
