@@ -67,7 +67,7 @@ def lib():
     L.fb_forward_f32.argtypes = [vp, i64, vp, vp, vp, vp]
     L.fb_pair_screen.argtypes = [vp, i64, vp, i32, vp, i32, vp, vp, vp, vp]
     L.fb_partition_screen.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, vp, vp, vp, vp, vp]
-    L.fb_partition_screen_ex.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.fb_partition_screen_ex.argtypes = [vp, i64, vp, vp, i32, u64, i64, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.fb_hybrid_predict.argtypes = [vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp]
     L.fb_profile_nearzero.argtypes = [vp, i64, vp, vp, i32, u64, i64, vp, vp, vp]
     L.fb_heuristic.argtypes = [vp, i64, vp, vp, vp, vp, vp, C.c_double, vp, vp, vp]

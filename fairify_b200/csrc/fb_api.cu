@@ -46,7 +46,7 @@ static int fb_fail(int code, const char *fmt, ...)
 extern "C" const char *fb_last_error(void) { return fb_err; }
 // for the library's other translation units (not part of the C ABI)
 void fb_set_error(const char *msg) { snprintf(fb_err, sizeof(fb_err), "%s", msg); }
-extern "C" int fb_version(void) { return 200; }
+extern "C" int fb_version(void) { return 210; }
 
 extern "C" int fb_num_sms(int *out)
 {
@@ -893,7 +893,7 @@ fb_ce_unpack_kernel(int64_t n, int d, int pa_col, bool relaxed, const int32_t *_
         int32_t cs = -1, vp = -1, vn = -1, dp = 0, dn = 0;
         uint8_t flag = 0;
         if (k == FB_SCREEN_SKIPPED) flag = FB_VERDICT_SKIPPED;
-        else if (k != ~0ull) {
+        else if (k != ~0ull && k != FB_SCREEN_NOSEARCH) {
             const int lo = boxes[p * (2 * d) + 2 * pa_col];
             cs = (int32_t)(k >> 32);
             if (relaxed) {
@@ -918,10 +918,19 @@ fb_ce_unpack_kernel(int64_t n, int d, int pa_col, bool relaxed, const int32_t *_
     }
 }
 
+// key[p] = "leave this box alone" where the caller's mask says so
+__global__ void __launch_bounds__(256)
+fb_screen_mark_kernel(int64_t n, const uint8_t *__restrict__ skip, unsigned long long *__restrict__ key)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride)
+        key[p] = skip[p] ? FB_SCREEN_NOSEARCH : ~0ull;
+}
+
 extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                                       uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_threshold,
                                       int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg,
-                                      uint8_t *verdict, uint32_t *record, void *stream)
+                                      uint8_t *verdict, uint32_t *record, const uint8_t *skip, void *stream)
 {
     if (int rc = fb_check_batch("fb_partition_screen", m, n, boxes, S, true)) return rc;
     const int d = m->gen.dims[0];
@@ -937,7 +946,13 @@ extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_
     fb_pick_chunks(m, n, S, &chunks, &chunk_len);
     DevBuf key(m->device, st);
     FB_CUDA(key.alloc(sizeof(unsigned long long) * n));
-    FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
+    if (skip) {
+        const int mgrid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)m->num_sms * 8);
+        fb_screen_mark_kernel<<<mgrid, 256, 0, st>>>(n, skip, (unsigned long long *)key.p);
+        FB_CUDA(cudaGetLastError());
+    } else {
+        FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
+    }
     if (fb_use_spec(m)) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));
@@ -972,7 +987,7 @@ extern "C" int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *
 {
     if (n > 0 && (!ce_sample || !pa_pos || !pa_neg)) return fb_fail(FB_ERR_INVALID, "fb_partition_screen: null output");
     return fb_partition_screen_ex(m, n, boxes, samples, S, seed, first_index, pa_col, -1, 0, ce_sample, pa_pos, pa_neg, nullptr,
-                                  nullptr, verdict, nullptr, stream);
+                                  nullptr, verdict, nullptr, nullptr, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------

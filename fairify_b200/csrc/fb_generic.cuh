@@ -455,7 +455,7 @@ template <int TM, bool PHILOX>
 __global__ void __launch_bounds__(FB_TILE_THREADS)
 fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict__ boxes,
                       const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp, int pa_col,
-                      int ra_col, int ra_thr, unsigned long long *__restrict__ ce_key)
+                      int ra_col, int ra_thr, unsigned long long *ce_key)
 {
     extern __shared__ __align__(16) unsigned char fb_smem[];
     float *buf0 = reinterpret_cast<float *>(fb_smem);
@@ -469,6 +469,7 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
     const bool relaxed = ra_col >= 0;
     const int nd = relaxed ? 2 * ra_thr + 1 : 1;                        // RA offsets per protected value
     for (int64_t p = blockIdx.x; p < n; p += gridDim.x) {
+        if (ce_key[p] == FB_SCREEN_NOSEARCH) continue;                   // (block-uniform: only this CTA touches ce_key[p])
         const int32_t *box = boxes + p * (2 * D0);
         const int pa_lo = __ldg(box + 2 * pa_col), pa_hi = __ldg(box + 2 * pa_col + 1);
         const uint32_t Wu = (uint32_t)(pa_hi - pa_lo + 1);
@@ -822,7 +823,7 @@ __global__ void __launch_bounds__(FB_PROFILE_THREADS)
 fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes,
                                const int32_t *__restrict__ samples, uint64_t seed, int64_t first_index, int nsamp,
                                int chunks, int chunk_len, int pa_col, int ra_col, int ra_thr,
-                               unsigned long long *__restrict__ ce_key)
+                               unsigned long long *ce_key)
 {
     const int D0 = net.dims[0];
     const int lane = threadIdx.x & 31;
@@ -833,6 +834,7 @@ fb_partition_screen_gen_kernel(const GenNet net, int64_t n, const int32_t *__res
     float x0[FB_MAXW], a[FB_MAXW], y[FB_MAXW];
     for (int64_t u = gwarp; u < units; u += nwarps) {
         const int64_t p = u / chunks;
+        if (ce_key[p] == FB_SCREEN_NOSEARCH) continue;
         const int c = (int)(u - p * chunks);
         const int s0 = c * chunk_len;
         const int s1 = min(nsamp, s0 + chunk_len);

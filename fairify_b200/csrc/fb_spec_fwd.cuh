@@ -216,6 +216,7 @@ fb_pair_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int
 // ranges over a - thr .. a + thr around the sample's own value a, unclipped.
 // ---------------------------------------------------------------------------------------------------
 #define FB_SCREEN_SKIPPED 0xfffffffffffffffeull     // key of a box whose protected range does not fit the key's fields
+#define FB_SCREEN_NOSEARCH 0xfffffffffffffffdull    // key pre-set by the caller's skip mask: the kernels leave the box alone
 #define FB_SCREEN_MAX_W_STRICT 65536u
 #define FB_SCREEN_MAX_W_RELAXED 256u
 #define FB_SCREEN_MAX_THR 127
@@ -262,7 +263,7 @@ __global__ void __launch_bounds__(FB_PROFILE_THREADS)
 fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int64_t n,
                                 const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
                                 int64_t first_index, int nsamp, int chunks, int chunk_len, int pa_col, int ra_col, int ra_thr,
-                                unsigned long long *__restrict__ ce_key)
+                                unsigned long long *ce_key)
 {
     constexpr int D0 = S::D0;
     const int lane = threadIdx.x & 31;
@@ -272,6 +273,7 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
     const bool relaxed = ra_col >= 0;
     for (int64_t u = gwarp; u < units; u += nwarps) {
         const int64_t p = u / chunks;
+        if (ce_key[p] == FB_SCREEN_NOSEARCH) continue;
         const int c = (int)(u - p * chunks);
         const int s0 = c * chunk_len;
         const int s1 = min(nsamp, s0 + chunk_len);

@@ -74,6 +74,8 @@ def prune_grid_sharded(model, grid, S=1000, seed=0, tol=None, n_total=None, grou
     r = model.prune(boxes, S=S, seed=seed, first_index=first, tol=tol, want=("record",))
     rec = r.t["record"]
     if pa_col is not None:
-        model.partition_screen(boxes, pa_col, S=S, seed=seed, first_index=first, record=rec)
+        # (boxes the bounds kernel certified one-signed cannot hold a counterexample pair: not searched)
+        certified = (rec[:, 0] & 1).to(torch.uint8)
+        model.partition_screen(boxes, pa_col, S=S, seed=seed, first_index=first, record=rec, skip=certified)
     full = allgather_records(rec, n_total, group)
     return unpack_records(full, model.NW)

@@ -302,11 +302,25 @@ class Model:
                                         _ptr(alts), _ptr(orig), _ptr(flip), _stream()), "fb_pair_screen")
         return orig, flip
 
+    def certified(self, boxes, ra_col=None, ra_threshold=0):
+        """uint8 [n]: 1 where the bounds kernel certifies the logit one-signed over the box -- over the box widened by
+        ra_threshold on both sides of column ra_col for a relaxed query -- i.e. where partition_screen need not search."""
+        boxes = self._dev(boxes, torch.int32)
+        if ra_col is not None and ra_col >= 0 and ra_threshold:
+            boxes = boxes.clone()
+            boxes[:, ra_col, 0] -= int(ra_threshold); boxes[:, ra_col, 1] += int(ra_threshold)
+        v = self.ibp(boxes, want=("verdict",)).t["verdict"]
+        return (v & VERDICT_CERTIFIED).to(torch.uint8)
+
     def partition_screen(self, boxes, pa_col, S=1000, samples=None, seed=0, first_index=0, verdict=None, ra_col=None,
-                         ra_threshold=0, record=None):
+                         ra_threshold=0, record=None, skip=None):
         """Sampled counterexample screen.  Returns [ce_sample, pa_pos, pa_neg] (int32 [n] each), plus [ra_dpos, ra_dneg]
-        when a relaxed column is given (relaxed/AC/Verify-AC.py:48-51); `record` = the packed records of prune()."""
+        when a relaxed column is given (relaxed/AC/Verify-AC.py:48-51); `record` = the packed records of prune();
+        `skip` = uint8 [n], non-zero where the box is not to be searched (see certified())."""
         boxes = self._dev(boxes, torch.int32); n = boxes.shape[0]
+        skip = self._dev(skip, torch.uint8)
+        if skip is not None and tuple(skip.shape) != (n,):
+            raise ValueError("partition_screen: skip must have one byte per box")
         samples = self._dev(samples, torch.int32)
         if samples is not None:
             S = samples.shape[1]
@@ -315,7 +329,8 @@ class Model:
         check(_lib.lib().fb_partition_screen_ex(self._h, n, _ptr(boxes), _ptr(samples), int(S), C.c_uint64(seed),
                                                 int(first_index), int(pa_col), int(ra_col) if relaxed else -1, int(ra_threshold),
                                                 _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(outs[3]) if relaxed else None,
-                                                _ptr(outs[4]) if relaxed else None, _ptr(verdict), _ptr(record), _stream()),
+                                                _ptr(outs[4]) if relaxed else None, _ptr(verdict), _ptr(record), _ptr(skip),
+                                                _stream()),
               "fb_partition_screen")
         return outs
 

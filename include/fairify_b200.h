@@ -171,11 +171,16 @@ int fb_partition_screen(const fb_model *m, int64_t n, const int32_t *boxes, cons
  *    protected value ascending -- with a partner of another protected value and the other class.
  *    ra_dpos / ra_dneg int32 [n] (may be NULL): the difference applied to the positive / negative point (0 for the point
  *    inside the box).  Any of ce_sample / pa_pos / pa_neg / verdict may be NULL.  record (may be NULL): the packed records
- *    fb_ibp wrote ([n][2*NW+2] uint32): the last word of each receives ce_sample, word 0 the verdict flags. */
+ *    fb_ibp wrote ([n][2*NW+2] uint32): the last word of each receives ce_sample, word 0 the verdict flags.
+ *    skip (uint8 [n], may be NULL): boxes with a non-zero byte are not searched and report no counterexample.  Meant for
+ *    boxes fb_ibp certified (FB_VERDICT_CERTIFIED: the logit is one-signed over the whole box, so no pair of points of
+ *    the box can differ in class): for a strict query pass the certified bit of the boxes themselves, for a relaxed one
+ *    that of the boxes widened by ra_threshold on both sides of column ra_col (the second point may leave the box
+ *    there).  The certificate is about the real-valued network; the screen evaluates in float32. */
 int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                            uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_threshold,
                            int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg,
-                           uint8_t *verdict, uint32_t *record, void *stream);
+                           uint8_t *verdict, uint32_t *record, const uint8_t *skip, void *stream);
 
 /* -- hybrid prediction: find_partition_result_for_point + hybrid_predict, src/AC/Verify-AC-experiment-new2.py:587-638.
  *    For each of `rows` points: the partition of grid g that contains it, that partition's recorded verdict

@@ -490,6 +490,46 @@ def test_relaxed_screen_with_a_sweep_wider_than_a_tile(eng, name, thr):
     assert all(np.array_equal(a.cpu().numpy(), b_) for a, b_ in zip(got2, want))
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-2", "AC-10", "AC-4"])
+def test_partition_screen_skip_mask_and_certified_boxes(eng, name):
+    """skip: masked boxes report no counterexample, the others are untouched (strict and relaxed, every kernel family).
+    certified(): a box the bounds kernel certifies one-signed -- widened on the relaxed column for a relaxed query --
+    holds no counterexample in the unmasked screen either, so masking it changes nothing."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    pa, ra, thr = dom.columns.index("race"), dom.columns.index("age"), 5
+    grid = eng.Grid(dom.columns, dom.ranges, 6)
+    n, S = (64, 40) if m.P > 4000 else (400, 60)
+    # a window that straddles the first certified box of the grid's first 20 000, if there is one
+    c0 = m.certified(grid.boxes(0, 20000)).cpu().numpy()
+    first = max(0, int(np.flatnonzero(c0)[0]) - n // 2) if c0.any() else 2 * len(grid) // 3
+    boxes = grid.boxes(first, n); hb = boxes.cpu().numpy()
+    samples = O.philox_samples(3, first, hb, S)
+    rng = np.random.default_rng(8)
+    for relaxed in (False, True):
+        kw = dict(ra_col=ra, ra_threshold=thr) if relaxed else {}
+        want = O.partition_screen_ex(net, samples, hb, pa, ra if relaxed else -1, thr if relaxed else 0)
+        nout = 5 if relaxed else 3
+        mask = (rng.random(n) < 0.4).astype(np.uint8)
+        verdict = torch.zeros((n,), dtype=torch.uint8, device="cuda")
+        got = [t.cpu().numpy() for t in m.partition_screen(boxes, pa, S=S, seed=3, first_index=first, skip=mask, verdict=verdict, **kw)]
+        none = (-1, -1, -1, 0, 0)
+        for k in range(nout):
+            assert np.array_equal(got[k], np.where(mask != 0, none[k], want[k])), (relaxed, k)
+        assert np.array_equal((verdict.cpu().numpy() & eng.VERDICT_CE) != 0, (want[0] >= 0) & (mask == 0))
+        cert = m.certified(boxes, **kw).cpu().numpy()
+        assert not (want[0][cert != 0] >= 0).any()                  # a certified box has no counterexample
+        got2 = [t.cpu().numpy() for t in m.partition_screen(boxes, pa, S=S, seed=3, first_index=first, skip=cert, **kw)]
+        for k in range(nout):
+            assert np.array_equal(got2[k], want[k]), (relaxed, k)
+    if name in ("AC-1", "AC-2", "AC-10"):
+        c = m.certified(boxes).cpu().numpy()                       # (these networks have certified boxes on this grid)
+        assert c.any() and not c.all()
+    with pytest.raises(Exception):
+        m.partition_screen(boxes, pa, S=S, skip=np.zeros(n + 1, dtype=np.uint8))
+
+
 def test_partition_screen_rejects_what_it_cannot_encode(eng):
     """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
     w, b = G.wb("GC-1")

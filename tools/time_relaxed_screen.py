@@ -16,4 +16,10 @@ for name in sys.argv[1:]:
             a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(); r = m.partition_screen(bx, D.columns.index("race"), S=1000, seed=1, **kw); e.record(); torch.cuda.synchronize()
         ce = r[0].cpu().numpy()
-        print(name, mode, f"{n/(a.elapsed_time(e)*1e-3):.4g} partitions/s", "ce frac", (ce>=0).mean(), flush=True)
+        for _ in range(2):
+            a2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a2.record(); cert = m.certified(bx, **kw)
+            r2 = m.partition_screen(bx, D.columns.index("race"), S=1000, seed=1, skip=cert, **kw); e2.record(); torch.cuda.synchronize()
+        assert all(torch.equal(x, y) for x, y in zip(r, r2))
+        print(name, mode, f"{n/(a.elapsed_time(e)*1e-3):.4g} partitions/s", "ce frac", (ce>=0).mean(),
+              f"| skipping certified ({float(cert.float().mean()):.3f}): {n/(a2.elapsed_time(e2)*1e-3):.4g} partitions/s", flush=True)
