@@ -75,6 +75,7 @@ struct fb_model {
     FbTileNet tile{};               // padded float64 weights for the tiled profile kernel
     double *dWpad = nullptr;
     float *dWpad32 = nullptr;
+    float *dWiv32 = nullptr;
     FbMmaNet mma{};                 // fragment-major weights for the DMMA profile kernel
     double *dWf = nullptr, *dBp = nullptr;
     uint32_t *dUnb = nullptr;       // per neuron: a non-zero weight on an input the singular-verification query leaves unbounded
@@ -135,7 +136,7 @@ extern "C" void fb_model_destroy(fb_model *m)
 {
     if (!m) return;
     if (m->spec) m->spec->free_params(m->p64, m->p32);
-    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32); cudaFree(m->dUnb); cudaFree(m->dWf); cudaFree(m->dBp);
+    cudaFree(m->dW64); cudaFree(m->dB64); cudaFree(m->dW32); cudaFree(m->dB32); cudaFree(m->dWpad); cudaFree(m->dWpad32); cudaFree(m->dWiv32); cudaFree(m->dUnb); cudaFree(m->dWf); cudaFree(m->dBp);
     delete m;
 }
 
@@ -222,7 +223,19 @@ extern "C" int fb_model_create(int L, const int32_t *dims, const float *w, const
         e = cudaMalloc(&m->dWpad32, sizeof(float) * wp32.size());
         if (e == cudaSuccess) e = cudaMemcpy(m->dWpad32, wp32.data(), sizeof(float) * wp32.size(), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
-        t.Wp = m->dWpad; t.B = m->dB64; t.Wp32 = m->dWpad32; t.B32 = m->dB32;
+        // the interval form of the float32 weights (fb_tile_forward_f32<.., true>): rows max(w_k, 0), min(w_k, 0) alternate
+        std::vector<float> wiv(2 * wp32.size(), 0.0f);
+        for (int l = 0; l < L; ++l)
+            for (int i = 0; i < g.dims[l]; ++i)
+                for (int j = 0; j < t.dimsp[l + 1]; ++j) {
+                    const float w = wp32[(size_t)t.woffp[l] + (size_t)i * t.dimsp[l + 1] + j];
+                    wiv[2 * (size_t)t.woffp[l] + (size_t)(2 * i) * t.dimsp[l + 1] + j] = w > 0.0f ? w : 0.0f;
+                    wiv[2 * (size_t)t.woffp[l] + (size_t)(2 * i + 1) * t.dimsp[l + 1] + j] = w < 0.0f ? w : 0.0f;
+                }
+        e = cudaMalloc(&m->dWiv32, sizeof(float) * wiv.size());
+        if (e == cudaSuccess) e = cudaMemcpy(m->dWiv32, wiv.data(), sizeof(float) * wiv.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { fb_model_destroy(m); return fb_fail(FB_ERR_CUDA, "fb_model_create: %s", cudaGetErrorString(e)); }
+        t.Wp = m->dWpad; t.B = m->dB64; t.Wp32 = m->dWpad32; t.Wiv32 = m->dWiv32; t.B32 = m->dB32;
     }
     {
         // weights in the operand order of the FP64 matrix instruction, columns of every tile permuted (fb_mma.cuh)
@@ -953,10 +966,11 @@ extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_
     } else {
         FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
     }
-    if (fb_use_spec(m)) {
+    const bool spec_screen = fb_use_spec(m) && (ra_col < 0 || m->gen.P <= FB_SCREEN_SPEC_RELAXED_MAXP);
+    if (spec_screen) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));
-    } else if (fb_use_tiled_profile(m)) {
+    } else if (fb_use_tiled_profile(m) || fb_use_spec(m)) {
         if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, ra_col, ra_threshold,
                                      (unsigned long long *)key.p, st)) return rc;
     } else {

@@ -97,6 +97,7 @@ struct FbTileNet {
     const double *Wp;                // [in][dimsp[l+1]] per layer, zero padded
     const double *B;
     const float *Wp32;               // the same in float32 (partition screen)
+    const float *Wiv32;              // rows (max(w_k, 0), min(w_k, 0)) interleaved: [2 in][dimsp[l+1]] per layer at 2 * woffp[l]
     const float *B32;
 };
 
@@ -318,22 +319,34 @@ fb_profile_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict
 // ---------------------------------------------------------------------------------------------------
 __host__ __device__ inline size_t fb_screen_tile_smem_bytes(int maxw, int maxwp, int TM)
 {
-    return sizeof(float) * (2 * (size_t)maxw * TM + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp) + 64;
+    // activations (two buffers), weight stages, the best key + state words, the relaxed screen's pending-sample list
+    return sizeof(float) * (2 * (size_t)maxw * TM + (size_t)FB_TILE_STAGES * FB_TILE_KC * maxwp) + 64 + sizeof(int) * (2 * (size_t)TM);
 }
 
-// all layers for the TM rows in buf0 (feature-major); returns the buffer whose first row holds the TM logits
-template <int TM>
+// all layers for the TM rows in buf0 (feature-major, `bufsz` floats per buffer); returns the buffer whose first feature
+// row holds the TM logits.  NJ = neurons per thread of the 4 x NJ register tile (8, or 4 to spread a small tile over all
+// warps).
+//
+// IV: the interval form.  Rows come in pairs (2s, 2s+1) = (lower, upper) end of sample s, and a layer with IN inputs
+// is a plain product over 2 IN features: the lower row holds (lo_0, hi_0, lo_1, hi_1, ...), the upper row
+// (hi_0, lo_0, hi_1, lo_1, ...), and the weight rows are (max(w_0, 0), min(w_0, 0), max(w_1, 0), ...) (Wiv32).  Of the two
+// terms of input k one is the product the ordinary pass would add (lower end: w_k lo_k if w_k >= 0, else w_k hi_k) and
+// the other is 0 * x, which leaves the sum as it is: each end is the same chain of round-to-nearest multiply-adds,
+// in the same order, as the ordinary pass -- so [lower, upper] encloses every logit that pass COMPUTES for inputs
+// between the ends (rounding is monotone).  The epilogue writes each neuron's two ends back in both orders.
+template <int TM, int NJ, bool IV>
 __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net, float *buf0, int bufsz, float *wst, int maxwp)
 {
-    constexpr int KC = FB_TILE_KC, MB = TM / 32;
+    constexpr int KC = FB_TILE_KC, MB = TM / 32, NB = 4 * NJ;           // a warp's block: 32 rows x NB neurons
+    static_assert(NJ == 4 || NJ == 8, "4 x 4 or 4 x 8 register tiles");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lane_m = lane & 7, lane_n = lane >> 3;
     for (int l = 0; l < net.L; ++l) {
-        const int IN = net.dims[l], OUT = net.dims[l + 1], OUTP = net.dimsp[l + 1];
+        const int IN = (IV ? 2 : 1) * net.dims[l], OUT = net.dims[l + 1], OUTP = net.dimsp[l + 1];
         const bool last = (l == net.L - 1);
         const float *Ain = buf0 + (l & 1) * bufsz;
         float *Aout = buf0 + ((l + 1) & 1) * bufsz;
-        const float *Wl = net.Wp32 + net.woffp[l];
+        const float *Wl = IV ? net.Wiv32 + 2 * (size_t)net.woffp[l] : net.Wp32 + net.woffp[l];
         if (OUT <= 8) {
             for (int t = tid; t < TM * OUT; t += FB_TILE_THREADS) {
                 const int mm = t % TM, nn = t / TM;
@@ -343,12 +356,18 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
 #pragma unroll 4
                 for (int k = 0; k < IN; ++k) acc = __fmaf_rn(__ldg(wp + (size_t)k * OUTP), ap[(size_t)k * TM], acc);
                 const float pre = __fadd_rn(acc, __ldg(net.B32 + net.boff[l] + nn));
-                Aout[(size_t)nn * TM + mm] = last ? pre : (fb_pos(pre) ? pre : 0.0f);
+                const float h = last ? pre : (fb_pos(pre) ? pre : 0.0f);
+                if (IV && !last) {
+                    Aout[(size_t)(2 * nn) * TM + mm] = h;                 // own end first in the own row ...
+                    Aout[(size_t)(2 * nn + 1) * TM + (mm ^ 1)] = h;       // ... and second in the partner row
+                } else {
+                    Aout[(size_t)nn * TM + mm] = h;
+                }
             }
             __syncthreads();
             continue;
         }
-        const int nblocks = MB * (OUTP / 32);
+        const int nblocks = MB * (OUTP / NB);
         const int nchunks = (IN + KC - 1) / KC;
         auto stage = [&](int c) {
             const int rows = min(KC, IN - c * KC);
@@ -361,12 +380,12 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
             const int blk = blk0 + warp;
             const bool active = blk < nblocks;
             const int mb = blk % MB, nb = blk / MB;
-            const int m0 = mb * 32 + lane_m * 4, n0 = nb * 32 + lane_n * 8;      // 4 adjacent rows, 8 adjacent neurons
-            float acc[4][8];
+            const int m0 = mb * 32 + lane_m * 4, n0 = nb * NB + lane_n * NJ;      // 4 adjacent rows, NJ adjacent neurons
+            float acc[4][NJ];
 #pragma unroll
             for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[r][j] = 0.0f;
+                for (int j = 0; j < NJ; ++j) acc[r][j] = 0.0f;
             stage(0);
             if (nchunks > 1) stage(1);
             for (int c = 0; c < nchunks; ++c) {
@@ -381,20 +400,24 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
 #pragma unroll 4
                     for (int k = 0; k < rows; ++k, ap += TM, wp += OUTP) {
                         const float4 a4 = *reinterpret_cast<const float4 *>(ap);
-                        const float4 w0 = reinterpret_cast<const float4 *>(wp)[0], w1 = reinterpret_cast<const float4 *>(wp)[1];
                         const float a[4] = {a4.x, a4.y, a4.z, a4.w};
-                        const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+                        float w[NJ];
+#pragma unroll
+                        for (int q = 0; q < NJ / 4; ++q) {
+                            const float4 w4 = reinterpret_cast<const float4 *>(wp)[q];
+                            w[4 * q] = w4.x; w[4 * q + 1] = w4.y; w[4 * q + 2] = w4.z; w[4 * q + 3] = w4.w;
+                        }
 #pragma unroll
                         for (int r = 0; r < 4; ++r)
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) acc[r][j] = __fmaf_rn(w[j], a[r], acc[r][j]);
+                            for (int j = 0; j < NJ; ++j) acc[r][j] = __fmaf_rn(w[j], a[r], acc[r][j]);
                     }
                 }
             }
             __syncthreads();
             if (!active) continue;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < NJ; ++j) {
                 const int nn = n0 + j;
                 if (nn < OUT) {
                     const float bj = __ldg(net.B32 + net.boff[l] + nn);
@@ -404,7 +427,12 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
                         const float pre = __fadd_rn(acc[r][j], bj);
                         h[r] = last ? pre : (fb_pos(pre) ? pre : 0.0f);
                     }
-                    *reinterpret_cast<float4 *>(Aout + (size_t)nn * TM + m0) = make_float4(h[0], h[1], h[2], h[3]);
+                    if (IV && !last) {
+                        *reinterpret_cast<float4 *>(Aout + (size_t)(2 * nn) * TM + m0) = make_float4(h[0], h[1], h[2], h[3]);
+                        *reinterpret_cast<float4 *>(Aout + (size_t)(2 * nn + 1) * TM + m0) = make_float4(h[1], h[0], h[3], h[2]);
+                    } else {
+                        *reinterpret_cast<float4 *>(Aout + (size_t)nn * TM + m0) = make_float4(h[0], h[1], h[2], h[3]);
+                    }
                 }
             }
         }
@@ -412,44 +440,6 @@ __device__ __forceinline__ const float *fb_tile_forward_f32(const FbTileNet &net
     }
     return buf0 + (net.L & 1) * bufsz;
 }
-
-// One sample's sweep, row by row in the order fb_screen_sample evaluates it: rows 0 .. W-1 are the strict sweep of the
-// protected column (RA offset 0), then, in relaxed mode, W rows per RA offset d = -thr .. thr without 0.  row() is fed
-// the logits in that order and ends with the same key fb_screen_sample returns; `done` says no later row matters.
-struct FbScreenScan {
-    int vp, vp2, vn, vn2;                    // first / second protected offset with a positive / negative logit, -1 = none
-    uint32_t low;                            // 0xffffffff: no counterexample (yet)
-    bool done;
-    __device__ __forceinline__ void begin() { vp = vp2 = vn = vn2 = -1; low = 0xffffffffu; done = false; }
-    __device__ __forceinline__ void row(int q, float y, int W, bool relaxed, int thr)
-    {
-        if (done) return;
-        const int k = q / W, off = q - k * W;
-        if (k == 0) {
-            if (y > 0.0f) { if (vp < 0) vp = off; else if (vp2 < 0) vp2 = off; }
-            if (y < 0.0f) { if (vn < 0) vn = off; else if (vn2 < 0) vn2 = off; }
-            if (off == W - 1) {
-                if (vp >= 0 && vn >= 0) {
-                    low = relaxed ? ((uint32_t)vp << 24) | ((uint32_t)vn << 16) | (128u << 8) | 128u
-                                  : ((uint32_t)vp << 16) | (uint32_t)vn;
-                    done = true;
-                } else if (!relaxed || (vp < 0) == (vn < 0)) {
-                    done = true;                                        // one sweep only, or no class at all
-                }
-            }
-            return;
-        }
-        int d = -thr + (k - 1);
-        if (d >= 0) ++d;
-        if (vp >= 0 && y < 0.0f) {
-            const int partner = (vp != off) ? vp : vp2;
-            if (partner >= 0) { low = ((uint32_t)partner << 24) | ((uint32_t)off << 16) | (128u << 8) | (uint32_t)(d + 128); done = true; }
-        } else if (vn >= 0 && y > 0.0f) {
-            const int partner = (vn != off) ? vn : vn2;
-            if (partner >= 0) { low = ((uint32_t)off << 24) | ((uint32_t)partner << 16) | ((uint32_t)(d + 128) << 8) | 128u; done = true; }
-        }
-    }
-};
 
 template <int TM, bool PHILOX>
 __global__ void __launch_bounds__(FB_TILE_THREADS)
@@ -503,13 +493,83 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
                 for (int i = 0; i < D0; ++i) col[(size_t)i * TM] = 0.0f;
             }
         };
-        if (R <= TM) {
+        if (R <= TM && relaxed) {
+            // Relaxed sweeps are W * (2 thr + 1) rows per sample, and a box without a pair has every sample swept to
+            // the end.  So each sample first goes through the network once as an INTERVAL (two rows: protected column
+            // over the box's range, relaxed column over a - thr .. a + thr, the other features at the sample's values;
+            // fb_tile_forward_f32<.., true>).  A one-signed enclosure of the logit means the sweep would find one class
+            // only.  The samples left over wait in `pend`, ascending, until they fill a tile of sweeps.
+            constexpr int TA = TM / 2, SA = TA / 2;                       // interval tile: TA rows = SA samples
+            const int spt = TM / R;                                       // whole sweeps per tile
+            int *pend = s_state + 4;                                      // up to spt - 1 + SA entries
+            int npend = 0, sb = 0;
+            while (sb < nsamp || npend > 0) {
+                if (sb < nsamp && npend < spt) {
+                    const int ns = min(SA, nsamp - sb);
+                    if (tid < TA) {
+                        float *col = buf0 + tid;
+                        const int s_row = sb + (tid >> 1);
+                        const bool upper = tid & 1;
+                        if ((tid >> 1) < ns) {
+                            if (PHILOX) fb_draw_row<float>(box, D0, grp, (uint32_t)s_row, pidx, seed, col, 2 * TA);
+                            else {
+                                const int32_t *row = samples + ((int64_t)p * nsamp + s_row) * D0;
+                                for (int i = 0; i < D0; ++i) col[(size_t)(2 * i) * TA] = (float)__ldg(row + i);
+                            }
+                            for (int i = 0; i < D0; ++i) {
+                                float lo_i = col[(size_t)(2 * i) * TA], hi_i = lo_i;
+                                if (i == pa_col) { lo_i = (float)pa_lo; hi_i = (float)pa_hi; }
+                                if (i == ra_col) { const int a = (int)lo_i; lo_i = (float)(a - ra_thr); hi_i = (float)(a + ra_thr); }
+                                col[(size_t)(2 * i) * TA] = upper ? hi_i : lo_i;
+                                col[(size_t)(2 * i + 1) * TA] = upper ? lo_i : hi_i;
+                            }
+                        } else {
+                            for (int i = 0; i < 2 * D0; ++i) col[(size_t)i * TA] = 0.0f;
+                        }
+                    }
+                    __syncthreads();
+                    const float *y = fb_tile_forward_f32<TA, 4, true>(net, buf0, bufsz, wst, maxwp);
+                    if (tid == 0) {
+                        int np = npend;
+                        for (int t = 0; t < ns; ++t)
+                            if (!(y[2 * t] > 0.0f || y[2 * t + 1] < 0.0f)) pend[np++] = sb + t;
+                        s_state[0] = np;
+                    }
+                    __syncthreads();
+                    npend = s_state[0];
+                    sb += SA;
+                    continue;
+                }
+                const int take = min(npend, spt);
+                if (tid < TM) {
+                    const bool exists = tid < take * R;
+                    fill(exists ? pend[tid / R] : 0, tid % R, exists);
+                }
+                __syncthreads();
+                const float *y = fb_tile_forward_f32<TM, 8, false>(net, buf0, bufsz, wst, maxwp);
+                if (tid < take) {
+                    FbScreenScan sc;
+                    sc.begin();
+                    for (int q = 0; q < R && !sc.done; ++q) sc.row(q, y[tid * R + q], W, relaxed, ra_thr);
+                    if (sc.low != 0xffffffffu)
+                        atomicMin(s_best, ((unsigned long long)(uint32_t)pend[tid] << 32) | (unsigned long long)sc.low);
+                }
+                __syncthreads();
+                if (*s_best != ~0ull) break;
+                const int rest = npend - take;
+                const int v = tid < rest ? pend[take + tid] : 0;
+                __syncthreads();
+                if (tid < rest) pend[tid] = v;
+                __syncthreads();
+                npend = rest;
+            }
+        } else if (R <= TM) {
             const int spt = TM / R;                                       // whole samples per tile
             for (int sbase = 0; sbase < nsamp; sbase += spt) {
                 const int ns = min(spt, nsamp - sbase);
                 if (tid < TM) fill(sbase + tid / R, tid % R, tid < ns * R);
                 __syncthreads();
-                const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
+                const float *y = fb_tile_forward_f32<TM, 8, false>(net, buf0, bufsz, wst, maxwp);
                 if (tid < ns) {
                     FbScreenScan sc;
                     sc.begin();
@@ -529,7 +589,7 @@ fb_screen_tile_kernel(const FbTileNet net, int64_t n, const int32_t *__restrict_
                     const int nq = min(TM, R - q0);
                     if (tid < TM) fill(s, q0 + tid, tid < nq);
                     __syncthreads();
-                    const float *y = fb_tile_forward_f32<TM>(net, buf0, bufsz, wst, maxwp);
+                    const float *y = fb_tile_forward_f32<TM, 8, false>(net, buf0, bufsz, wst, maxwp);
                     if (tid == 0) {
                         for (int t = 0; t < nq && !sc.done; ++t) sc.row(q0 + t, y[t], W, relaxed, ra_thr);
                         if (sc.done) {

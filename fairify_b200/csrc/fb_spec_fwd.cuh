@@ -83,6 +83,39 @@ __device__ __forceinline__ T fb_spec_forward(const PRM &prm, const T (&x)[S::dim
     }
 }
 
+// Interval of float32 values for the screens' one-pass enclosure.  fb_fma / fb_add apply the forward pass's own
+// round-to-nearest operation to both ends (rounding is monotone: for x in [x.lo, x.hi] and acc in [acc.lo, acc.hi] the
+// computed fma(w, x, acc) lies between the two results), so fb_spec_forward on FbIv encloses every value the float
+// forward pass computes for inputs inside the input intervals -- computed values, not real-arithmetic ones.
+struct FbIv {
+    float lo, hi;
+    __device__ __forceinline__ FbIv() {}
+    __device__ __forceinline__ explicit FbIv(double v) : lo((float)v), hi((float)v) {}
+};
+__device__ __forceinline__ FbIv fb_fma(float w, const FbIv &x, const FbIv &acc)
+{
+    FbIv r;
+    const bool up = w >= 0.0f;
+    r.lo = __fmaf_rn(w, up ? x.lo : x.hi, acc.lo);
+    r.hi = __fmaf_rn(w, up ? x.hi : x.lo, acc.hi);
+    return r;
+}
+__device__ __forceinline__ FbIv fb_add(const FbIv &a, float b)
+{
+    FbIv r;
+    r.lo = __fadd_rn(a.lo, b); r.hi = __fadd_rn(a.hi, b);
+    return r;
+}
+struct FbIvReluVisit {
+    __device__ __forceinline__ FbIv neuron(int, bool last, const FbIv &pre)
+    {
+        if (last) return pre;
+        FbIv r;
+        r.lo = fb_pos(pre.lo) ? pre.lo : 0.0f; r.hi = fb_pos(pre.hi) ? pre.hi : 0.0f;
+        return r;
+    }
+};
+
 // plain ReLU visitor (logit only)
 template <typename T>
 struct FbReluVisit {
@@ -227,38 +260,67 @@ fb_pair_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int
 // first (delta ascending from -thr, protected value ascending) second point of the other class that has a partner of
 // a different protected value in the strict sweep (low word = off_pos << 24 | off_neg << 16 | (dpos+128) << 8 | (dneg+128),
 // d* = RA offset of that point, 0 for the one inside the partition).  0xffffffff: no counterexample in this sample.
+// One sample's sweep, row by row: rows 0 .. W-1 are the strict sweep of the protected column (RA offset 0), then, in
+// relaxed mode, W rows per RA offset d = -thr .. thr without 0.  row() is fed the logits in that order; `low` ends as
+// the key described above fb_screen_sample, `done` says no later row matters.
+struct FbScreenScan {
+    int vp, vp2, vn, vn2;                    // first / second protected offset with a positive / negative logit, -1 = none
+    uint32_t low;                            // 0xffffffff: no counterexample (yet)
+    bool done;
+    __device__ __forceinline__ void begin() { vp = vp2 = vn = vn2 = -1; low = 0xffffffffu; done = false; }
+    // k = 0: strict sweep; k >= 1: the k-th relaxed offset d
+    __device__ __forceinline__ void row(int k, int off, int d, float y, int W, bool relaxed)
+    {
+        if (done) return;
+        if (k == 0) {
+            if (y > 0.0f) { if (vp < 0) vp = off; else if (vp2 < 0) vp2 = off; }
+            if (y < 0.0f) { if (vn < 0) vn = off; else if (vn2 < 0) vn2 = off; }
+            if (off == W - 1) {
+                if (vp >= 0 && vn >= 0) {
+                    low = relaxed ? ((uint32_t)vp << 24) | ((uint32_t)vn << 16) | (128u << 8) | 128u
+                                  : ((uint32_t)vp << 16) | (uint32_t)vn;
+                    done = true;
+                } else if (!relaxed || (vp < 0) == (vn < 0)) {
+                    done = true;                                        // one sweep only, or no class at all
+                }
+            }
+            return;
+        }
+        if (vp >= 0 && y < 0.0f) {
+            const int partner = (vp != off) ? vp : vp2;
+            if (partner >= 0) { low = ((uint32_t)partner << 24) | ((uint32_t)off << 16) | (128u << 8) | (uint32_t)(d + 128); done = true; }
+        } else if (vn >= 0 && y > 0.0f) {
+            const int partner = (vn != off) ? vn : vn2;
+            if (partner >= 0) { low = ((uint32_t)off << 24) | ((uint32_t)partner << 16) | ((uint32_t)(d + 128) << 8) | 128u; done = true; }
+        }
+    }
+    // row q of the sweep, q = k * W + off
+    __device__ __forceinline__ void row(int q, float y, int W, bool relaxed, int thr)
+    {
+        const int k = q / W, off = q - k * W;
+        int d = k == 0 ? 0 : -thr + (k - 1);
+        if (k != 0 && d >= 0) ++d;
+        row(k, off, d, y, W, relaxed);
+    }
+};
+
 template <class Eval>
 __device__ __forceinline__ uint32_t fb_screen_sample(Eval &ev, int pa_lo, uint32_t W, bool relaxed, int ra_val, int thr)
 {
-    bool havep = false, haven = false;
-    int vp = 0, vn = 0, vp2 = -1, vn2 = -1;
-    for (uint32_t off = 0; off < W; ++off) {
-        const float y = ev(pa_lo + (int)off, ra_val);
-        if (y > 0.0f) { if (!havep) { havep = true; vp = (int)off; } else if (vp2 < 0) vp2 = (int)off; }
-        if (y < 0.0f) { if (!haven) { haven = true; vn = (int)off; } else if (vn2 < 0) vn2 = (int)off; }
+    // (one loop over all rows, so that the network is inlined once)
+    FbScreenScan sc;
+    sc.begin();
+    const int nk = relaxed ? 2 * thr + 1 : 1;
+    int d = 0;
+    for (int k = 0; k < nk && !sc.done; ++k) {
+        for (int off = 0; off < (int)W && !sc.done; ++off)
+            sc.row(k, off, d, ev(pa_lo + off, ra_val + d), (int)W, relaxed);
+        d = (k == 0) ? -thr : (d + 1 == 0 ? 1 : d + 1);
     }
-    if (havep && haven)
-        return relaxed ? ((uint32_t)vp << 24) | ((uint32_t)vn << 16) | (128u << 8) | 128u : ((uint32_t)vp << 16) | (uint32_t)vn;
-    if (relaxed && havep != haven) {
-        for (int d = -thr; d <= thr; ++d) {
-            if (d == 0) continue;
-            for (uint32_t off = 0; off < W; ++off) {
-                const float y = ev(pa_lo + (int)off, ra_val + d);
-                if (havep && y < 0.0f) {
-                    const int partner = (vp != (int)off) ? vp : vp2;
-                    if (partner >= 0) return ((uint32_t)partner << 24) | (off << 16) | (128u << 8) | (uint32_t)(d + 128);
-                }
-                if (haven && y > 0.0f) {
-                    const int partner = (vn != (int)off) ? vn : vn2;
-                    if (partner >= 0) return (off << 24) | ((uint32_t)partner << 16) | ((uint32_t)(d + 128) << 8) | 128u;
-                }
-            }
-        }
-    }
-    return 0xffffffffu;
+    return sc.low;
 }
 
-template <class S, bool PHILOX>
+template <class S, bool PHILOX, bool RELAXED>
 __global__ void __launch_bounds__(FB_PROFILE_THREADS)
 fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm, int64_t n,
                                 const int32_t *__restrict__ boxes, const int32_t *__restrict__ samples, uint64_t seed,
@@ -270,7 +332,7 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t units = n * chunks;
-    const bool relaxed = ra_col >= 0;
+    constexpr bool relaxed = RELAXED;                    // (the launcher picks the instantiation from ra_col >= 0)
     for (int64_t u = gwarp; u < units; u += nwarps) {
         const int64_t p = u / chunks;
         if (ce_key[p] == FB_SCREEN_NOSEARCH) continue;
@@ -300,19 +362,56 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
         const int grp = fb_draw_group(widest);
         const int64_t pidx = first_index + p;
         unsigned long long best = ~0ull;
-        for (int sb = s0; sb < s1; sb += 32) {
-            const int s = sb + lane;
-            const bool active = s < s1;
-            float x0[D0];
+        // sample s of this partition as float32 features (s_src: the row to read when samples are injected)
+        auto load = [&](int s, int s_src, float (&x0)[D0]) {
             if (PHILOX) {
                 if (grp == 4) fb_draw_spec<D0, 1, 4>(lo, range, s, pidx, seed, x0);
                 else if (grp == 2) fb_draw_spec<D0, 1, 2>(lo, range, s, pidx, seed, x0);
                 else fb_draw_spec<D0, 1, 1>(lo, range, s, pidx, seed, x0);
             } else {
-                const int32_t *row = samples + ((int64_t)p * nsamp + (active ? s : s0)) * D0;
+                const int32_t *row = samples + ((int64_t)p * nsamp + s_src) * D0;
 #pragma unroll
                 for (int i = 0; i < D0; ++i) x0[i] = (float)__ldg(row + i);
             }
+        };
+        // Relaxed queries sweep W * (2 thr + 1) points per sample, and in a box without a pair every sample is swept to
+        // the end.  So each sample first goes through the network ONCE as an interval: protected column over the box's
+        // range, relaxed column over a - thr .. a + thr, the other features at the sample's values (fb_spec_forward on
+        // FbIv: the same multiply-adds in the same order on both ends, which encloses every logit the sweep would
+        // compute, rounding included).  A one-signed enclosure means the sweep finds one class only: no pair in this
+        // sample.  The others wait in `pend` (ascending) until 32 of them fill a sweep step.
+        __shared__ int s_pend[FB_PROFILE_THREADS / 32][64];
+        int *pend = s_pend[threadIdx.x >> 5];
+        int npend = 0, sb = s0;
+        while (sb < s1 || npend > 0) {
+            if (relaxed && sb < s1 && npend < 32) {
+                const int s = sb + lane;
+                const bool active = s < s1;
+                float x0[D0];
+                load(s, active ? s : s0, x0);
+                FbIv xi[D0];
+#pragma unroll
+                for (int i = 0; i < D0; ++i) {
+                    xi[i].lo = xi[i].hi = x0[i];
+                    if (i == pa_col) { xi[i].lo = (float)pa_lo; xi[i].hi = (float)(pa_lo + (int)W - 1); }
+                    if (i == ra_col) { const int a = (int)x0[i]; xi[i].lo = (float)(a - ra_thr); xi[i].hi = (float)(a + ra_thr); }
+                }
+                FbIvReluVisit vis;
+                const FbIv y = fb_spec_forward<S, 0, FbIv>(prm, xi, vis);
+                const bool open = active && !(y.lo > 0.0f || y.hi < 0.0f);
+                const uint32_t m = __ballot_sync(0xffffffffu, open);
+                if (open) pend[npend + __popc(m & ((1u << lane) - 1u))] = s;
+                npend += __popc(m);
+                sb += 32;
+                __syncwarp();
+                continue;
+            }
+            int s;
+            bool active;
+            if (relaxed) { active = lane < npend; s = active ? pend[lane] : s0; }
+            else { s = sb + lane; active = s < s1; sb += 32; }
+            float x0[D0];
+            load(s, active ? s : s0, x0);
             int ra_val = 0;
 #pragma unroll
             for (int i = 0; i < D0; ++i)
@@ -328,6 +427,14 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
             const bool ce = active && low != 0xffffffffu;
             if (ce && best == ~0ull) best = ((unsigned long long)(uint32_t)s << 32) | low;
             if (__any_sync(0xffffffffu, ce)) break;          // later samples cannot beat this step's
+            if (relaxed) {
+                const int rest = npend > 32 ? npend - 32 : 0;
+                const int v = lane < rest ? pend[32 + lane] : 0;
+                __syncwarp();
+                if (lane < rest) pend[lane] = v;
+                __syncwarp();
+                npend = rest;
+            }
         }
         // lowest sample index wins; keys are unique per sample so min over the packed key is enough
         const uint32_t hi = (uint32_t)(best >> 32);

@@ -69,14 +69,22 @@ struct FbSpecFwdOps {
     {
         const P32 &prm = *static_cast<const P32 *>(p32);
         const int64_t ctas = (n * chunks + (FB_PROFILE_THREADS / 32) - 1) / (FB_PROFILE_THREADS / 32);
-        if (philox) {
-            auto k = fb_partition_screen_spec_kernel<S, true>;
+        auto launch = [&](auto k) {
             k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
                 prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ra_col, ra_thr, ce_key);
+        };
+        if (ra_col >= 0) {
+            // (relaxed queries of the bigger architectures go to the tiled runtime-shape screen, fb_api.cu: their fully
+            // unrolled sweep + interval pass would take ten minutes each to compile)
+            if constexpr (S::P <= FB_SCREEN_SPEC_RELAXED_MAXP) {
+                if (philox) launch(fb_partition_screen_spec_kernel<S, true, true>);
+                else launch(fb_partition_screen_spec_kernel<S, false, true>);
+            } else {
+                return cudaErrorNotSupported;
+            }
         } else {
-            auto k = fb_partition_screen_spec_kernel<S, false>;
-            k<<<fb_grid_for(k, FB_PROFILE_THREADS, 0, ctas, num_sms), FB_PROFILE_THREADS, 0, st>>>(
-                prm, n, boxes, samples, seed, first_index, nsamp, chunks, chunk_len, pa_col, ra_col, ra_thr, ce_key);
+            if (philox) launch(fb_partition_screen_spec_kernel<S, true, false>);
+            else launch(fb_partition_screen_spec_kernel<S, false, false>);
         }
         return cudaGetLastError();
     }

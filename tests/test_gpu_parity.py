@@ -434,7 +434,7 @@ def test_partition_screen_matches_oracle(eng, name):
             assert ya > 0 and yb < 0
 
 
-@pytest.mark.parametrize("name", ["AC-1", "AC-3", "AC-5", "AC-4", "AC-10"])
+@pytest.mark.parametrize("name", ["AC-1", "AC-3", "AC-5", "AC-4", "AC-10", "AC-7", "AC-2"])
 def test_relaxed_partition_screen_matches_oracle(eng, name):
     """relaxed/AC query (PA = race, RA = age, threshold 5; relaxed/AC/Verify-AC.py:48-51): counterexample sample, protected
     values and the difference applied to the relaxed column, bit for bit against the oracle; every reported pair is
