@@ -970,7 +970,8 @@ extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_
     if (spec_screen) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));
-    } else if (fb_use_tiled_profile(m) || fb_use_spec(m)) {
+    } else if (fb_use_tiled_profile(m) || fb_use_spec(m) || ra_col >= 0) {
+        // (every relaxed query without a specialised kernel: the tiled screen has the interval pass, the sample-per-lane one not)
         if (int rc = fb_screen_tiled(m, n, boxes, samples, S, seed, first_index, pa_col, ra_col, ra_threshold,
                                      (unsigned long long *)key.p, st)) return rc;
     } else {

@@ -530,6 +530,36 @@ def test_partition_screen_skip_mask_and_certified_boxes(eng, name):
         m.partition_screen(boxes, pa, S=S, skip=np.zeros(n + 1, dtype=np.uint8))
 
 
+@pytest.mark.parametrize("dims", [(13, 16, 8, 1), (13, 100, 100, 1), (13, 40, 24, 1)])
+def test_relaxed_screen_on_networks_with_logits_at_the_rounding_level(eng, dims):
+    """The interval pass that precedes a relaxed sweep must never set aside a sample whose sweep shows two classes, also
+    where the logits are within float32 rounding of zero: random networks whose output bias cancels the typical logit
+    (specialised kernel, tiled kernel, sample-per-lane kernel), against the oracle's full sweep."""
+    rng = np.random.default_rng(sum(dims))
+    dom = G.domain("AC-1")
+    w = [(rng.standard_normal((dims[k], dims[k + 1])) / np.sqrt(dims[k])).astype(np.float32) for k in range(len(dims) - 1)]
+    b = [(0.1 * rng.standard_normal(dims[k + 1])).astype(np.float32) for k in range(len(dims) - 1)]
+    pa, ra, thr = dom.columns.index("race"), dom.columns.index("age"), 5
+    grid = None
+    for scale in (1.0, 1e-3):                       # second round: last layer scaled down, logits ~1e-3 of the first
+        w[-1] = (w[-1] * np.float32(scale)).astype(np.float32)
+        net0 = O.Net(w, b)
+        m0 = eng.Model(w, b)
+        grid = eng.Grid(dom.columns, dom.ranges, 6)
+        first, n, S = len(grid) // 7, 96, 24
+        boxes = grid.boxes(first, n); hb = boxes.cpu().numpy()
+        samples = O.philox_samples(2, first, hb, S)
+        y = O.forward_f32(net0, samples.reshape(-1, dims[0]).astype(np.float32))
+        b[-1] = (b[-1] - np.float32(np.median(y))).astype(np.float32)      # half of the sampled logits on either side of 0
+        net = O.Net(w, b); m = eng.Model(w, b)
+        want = O.partition_screen_ex(net, samples, hb, pa, ra, thr)
+        got = m.partition_screen(boxes, pa, S=S, seed=2, first_index=first, ra_col=ra, ra_threshold=thr)
+        for g_, w_, key in zip(got, want, ("ce_sample", "pa_pos", "pa_neg", "ra_dpos", "ra_dneg")):
+            assert np.array_equal(g_.cpu().numpy(), w_), (key, scale)
+        assert (want[0] >= 0).any()
+        del m0
+
+
 def test_partition_screen_rejects_what_it_cannot_encode(eng):
     """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
     w, b = G.wb("GC-1")
