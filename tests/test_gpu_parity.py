@@ -560,6 +560,30 @@ def test_relaxed_screen_on_networks_with_logits_at_the_rounding_level(eng, dims)
         del m0
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-5"])
+def test_relaxed_screen_edge_cases(eng, name):
+    """Threshold 0 (a relaxed query with nothing to relax: the strict pairs, relaxed output format), one sample per box,
+    a sample count that is not a multiple of anything, a single box, and no box at all."""
+    w, b = G.wb(name)
+    m = eng.Model(w, b); net = O.Net(w, b)
+    dom = G.domain(name)
+    pa, ra = dom.columns.index("race"), dom.columns.index("age")
+    grid = eng.Grid(dom.columns, dom.ranges, 6)
+    first = len(grid) // 2
+    for n, S, thr in ((40, 33, 0), (40, 1, 5), (1, 77, 3), (37, 5, 1)):
+        boxes = grid.boxes(first, n); hb = boxes.cpu().numpy()
+        samples = O.philox_samples(9, first, hb, S)
+        want = O.partition_screen_ex(net, samples, hb, pa, ra, thr)
+        got = m.partition_screen(boxes, pa, S=S, seed=9, first_index=first, ra_col=ra, ra_threshold=thr)
+        for g_, w_, key in zip(got, want, ("ce_sample", "pa_pos", "pa_neg", "ra_dpos", "ra_dneg")):
+            assert np.array_equal(g_.cpu().numpy(), w_), (key, n, S, thr)
+        if thr == 0:
+            strict = O.partition_screen(net, samples, hb, pa)
+            assert np.array_equal(want[0], strict[0]) and not want[3].any() and not want[4].any()
+    empty = m.partition_screen(grid.boxes(first, 0), pa, S=8, seed=1, ra_col=ra, ra_threshold=2)
+    assert all(t.numel() == 0 for t in empty)
+
+
 def test_partition_screen_rejects_what_it_cannot_encode(eng):
     """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
     w, b = G.wb("GC-1")
