@@ -515,6 +515,56 @@ def hybrid_case():
     print("hybrid case: routes", np.bincount(out["route"], minlength=4), "counters", out["counters"])
 
 
+def relaxed_case():
+    """The relaxed fairness property exactly as relaxed/AC/Verify-AC.py:122-132 assembles it for one partition --
+    in_const_adult ('neq' on the protected attribute, 'eq' on the others), in_const_diff_adult on the relaxed attribute,
+    in_const_domain_adult on the partition (utils/verif_utils.py:1065-1091, :859-867, :781-799) -- evaluated by Z3 on
+    concrete pairs of points: python tests/golden/make_golden.py relaxed  ->  tests/golden/relaxed_case.npz"""
+    import importlib
+    import z3
+    ref = refshim.load()
+    vu = importlib.import_module("utils.verif_utils")
+    D = domains.DOMAINS["AC"]
+    df = pd.DataFrame(np.zeros((2, D.d + 1)), columns=D.columns + ["income-per-year"])
+    rd = D.copy_ranges()                                                  # the ranges of relaxed/AC/Verify-AC.py:36-48
+    PA, RA, thr = ["race"], ["age"], 5                                    # :50-53
+    p_list = ref.input_partition.partitioned_ranges(rd.keys(), PA, ref.input_partition.partition(rd, 6), rd)
+    rng = np.random.RandomState(33)
+    boxes, X, X2, ok = [], [], [], []
+    x = np.array([z3.Int("x%s" % i) for i in range(D.d)]); x_ = np.array([z3.Int("x_%s" % i) for i in range(D.d)])
+    pa, ra = D.columns.index("race"), D.columns.index("age")
+    for pidx in rng.choice(len(p_list), 6, replace=False):
+        p = p_list[int(pidx)]
+        props = []
+        for attr in rd.keys():
+            if attr in PA:
+                props.extend(vu.in_const_adult(df, x, attr, "neq", x_))
+            elif attr in RA:
+                props.extend(vu.in_const_diff_adult(df, x, x_, attr, thr))
+            else:
+                props.extend(vu.in_const_adult(df, x, attr, "eq", x_))
+        props.extend(vu.in_const_domain_adult(df, x, x_, p, PA))
+        prop = z3.And(*props)
+        box = box_array(p, D.columns)
+        for k in range(120):
+            a = rng.randint(box[:, 0], box[:, 1] + 1)
+            if k % 9 == 0:                                                # first point outside the partition
+                c = rng.randint(D.d); a[c] = box[c, 1] + 1 + rng.randint(3)
+            b = a.copy()
+            b[pa] = rng.randint(-1, 7)                                    # protected value: same, other, or out of range
+            b[ra] = a[ra] + rng.randint(-7, 8)                            # relaxed attribute: within or beyond the threshold
+            if k % 5 == 0:                                                # some other attribute differs
+                c = rng.choice([i for i in range(D.d) if i not in (pa, ra)]); b[c] += 1
+            sub = [(x[i], z3.IntVal(int(a[i]))) for i in range(D.d)] + [(x_[i], z3.IntVal(int(b[i]))) for i in range(D.d)]
+            val = z3.simplify(z3.substitute(prop, *sub))
+            assert z3.is_true(val) or z3.is_false(val)
+            boxes.append(box); X.append(a); X2.append(b); ok.append(z3.is_true(val))
+    out = {"box": np.array(boxes, dtype=np.int32), "x": np.array(X, dtype=np.int64), "x2": np.array(X2, dtype=np.int64),
+           "admissible": np.array(ok, dtype=np.uint8), "pa": np.int64(pa), "ra": np.int64(ra), "thr": np.int64(thr)}
+    np.savez_compressed(os.path.join(HERE, "relaxed_case.npz"), **out)
+    print("relaxed case:", len(ok), "pairs,", int(np.sum(ok)), "admissible")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "hybrid":
         hybrid_case()
@@ -522,5 +572,7 @@ if __name__ == "__main__":
         singular_cases()
     elif len(sys.argv) > 1 and sys.argv[1] == "sliver":
         sliver_case()
+    elif len(sys.argv) > 1 and sys.argv[1] == "relaxed":
+        relaxed_case()
     else:
         main()

@@ -296,6 +296,26 @@ def test_hybrid_predict_matches_reference_functions():
     assert np.array_equal(logit > 0, z["pred"] > 0.5)
 
 
+def test_relaxed_pairs_are_the_ones_the_reference_property_admits():
+    """tests/golden/relaxed_case.npz: 720 concrete pairs judged by the property relaxed/AC/Verify-AC.py:122-132 builds
+    with the reference's own in_const_adult / in_const_diff_adult / in_const_domain_adult (Z3, make_golden.py relaxed).
+    The set the screen enumerates -- and test_relaxed_screen_restatement brute-forces -- must be that set: first point
+    in the box, second point equal to it except for another protected value inside the box's protected range and a
+    relaxed attribute at most `thr` away (not confined to the box)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "relaxed_case.npz"))
+    box, x, x2 = z["box"].astype(np.int64), z["x"], z["x2"]
+    pa, ra, thr = int(z["pa"]), int(z["ra"]), int(z["thr"])
+    other = np.ones(x.shape[1], dtype=bool); other[[pa, ra]] = False
+    rule = (np.all((x >= box[:, :, 0]) & (x <= box[:, :, 1]), axis=1)
+            & (x2[:, pa] >= box[:, pa, 0]) & (x2[:, pa] <= box[:, pa, 1]) & (x2[:, pa] != x[:, pa])
+            & (np.abs(x2[:, ra] - x[:, ra]) <= thr)
+            & np.all(x2[:, other] == x[:, other], axis=1))
+    assert np.array_equal(rule, z["admissible"] != 0)
+    assert 100 < rule.sum() < len(rule) - 100                       # both answers well represented
+    beyond = rule & ((x2[:, ra] < box[:, ra, 0]) | (x2[:, ra] > box[:, ra, 1]))
+    assert beyond.any()                                             # second points outside the box on the relaxed attribute
+
+
 def test_relaxed_screen_restatement():
     """The relaxed screen against a brute-force enumeration of the property the relaxed drivers give Z3
     (relaxed/AC/Verify-AC.py:128-132): x in the box, x' equal to x except on the protected column (different value, inside
