@@ -213,6 +213,10 @@ __device__ __forceinline__ VecD<K> fb_add(const VecD<K> &a, double b)
     return r;
 }
 
+// Specialised architectures above this many weights: relaxed partition screens run on the tiled runtime-shape kernel and
+// the strict ones carry no interval pass (the fully unrolled interval forward takes minutes per kernel to compile)
+#define FB_SCREEN_SPEC_RELAXED_MAXP 1500
+
 // verdict byte
 #define FB_VERDICT_CERTIFIED 1u     // output logit provably one-signed over the box (outward-rounded enclosure)
 #define FB_VERDICT_CE        2u     // sampled counterexample pair found by the partition screen

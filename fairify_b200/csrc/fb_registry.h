@@ -3,8 +3,6 @@
 // slow to build).  The C-ABI layer (fb_api.cu) looks a model's layer widths up here at fb_model_create time and falls
 // back to the runtime-shape kernels when there is no row.
 #pragma once
-// relaxed partition screens of specialised architectures above this many weights run on the tiled runtime-shape kernel
-#define FB_SCREEN_SPEC_RELAXED_MAXP 1500
 #include <cuda_runtime.h>
 #include <stdint.h>
 

@@ -383,8 +383,18 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
         __shared__ int s_pend[FB_PROFILE_THREADS / 32][64];
         int *pend = s_pend[threadIdx.x >> 5];
         int npend = 0, sb = s0;
+        // The same enclosure once for the WHOLE box (every feature over its range, the relaxed column widened by thr)
+        // before any sample is drawn: one-signed means no sample of this box can show two classes.  Only with generated
+        // samples (injected ones are the caller's and need not lie in the box), only for the smaller architectures (the
+        // strict kernels of the big ones would otherwise carry an interval pass just for this), and not for boxes whose
+        // ranges do not fit the arithmetic below.
+        bool boxdone = !(PHILOX && S::P <= FB_SCREEN_SPEC_RELAXED_MAXP);
+#pragma unroll
+        for (int i = 0; i < D0; ++i)
+            if (range[i] == 0u || lo[i] < -(1 << 30) || lo[i] > (1 << 30) || range[i] > (1u << 30)) boxdone = true;
         while (sb < s1 || npend > 0) {
-            if (relaxed && sb < s1 && npend < 32) {
+            if ((relaxed && sb < s1 && npend < 32) || !boxdone) {
+                const bool boxpass = !boxdone;
                 const int s = sb + lane;
                 const bool active = s < s1;
                 float x0[D0];
@@ -395,9 +405,18 @@ fb_partition_screen_spec_kernel(const __grid_constant__ SpecParams<S, float> prm
                     xi[i].lo = xi[i].hi = x0[i];
                     if (i == pa_col) { xi[i].lo = (float)pa_lo; xi[i].hi = (float)(pa_lo + (int)W - 1); }
                     if (i == ra_col) { const int a = (int)x0[i]; xi[i].lo = (float)(a - ra_thr); xi[i].hi = (float)(a + ra_thr); }
+                    if (boxpass) {
+                        const int w = (relaxed && i == ra_col) ? ra_thr : 0;
+                        xi[i].lo = (float)(lo[i] - w); xi[i].hi = (float)(lo[i] + (int)(range[i] - 1u) + w);
+                    }
                 }
                 FbIvReluVisit vis;
                 const FbIv y = fb_spec_forward<S, 0, FbIv>(prm, xi, vis);
+                if (boxpass) {
+                    boxdone = true;
+                    if (y.lo > 0.0f || y.hi < 0.0f) break;           // (the same for every lane: the box, not a sample)
+                    continue;
+                }
                 const bool open = active && !(y.lo > 0.0f || y.hi < 0.0f);
                 const uint32_t m = __ballot_sync(0xffffffffu, open);
                 if (open) pend[npend + __popc(m & ((1u << lane) - 1u))] = s;
