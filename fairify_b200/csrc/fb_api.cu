@@ -940,6 +940,67 @@ fb_screen_mark_kernel(int64_t n, const uint8_t *__restrict__ skip, unsigned long
         key[p] = skip[p] ? FB_SCREEN_NOSEARCH : ~0ull;
 }
 
+// The float32 enclosure of the logit over a whole box, for the screen kernels that do not compute it themselves (the
+// tiled and sample-per-lane ones, the specialised ones of the bigger architectures): one warp per box, lanes = neurons,
+// the screens' own arithmetic -- multiply-adds in ascending input order from 0, round to nearest, bias last -- on both
+// ends of the interval, which encloses every logit the screen would COMPUTE for a point of the box (rounding is
+// monotone).  One-signed: no sample of the box can show two classes, key[p] = "leave alone".  For a relaxed query the
+// relaxed column is widened by the threshold on both sides.  Generated samples only.
+#define FB_BOX_WARPS 8
+__global__ void __launch_bounds__(FB_BOX_WARPS * 32)
+fb_screen_box_kernel(const GenNet net, int64_t n, const int32_t *__restrict__ boxes, int pa_col, int ra_col, int ra_thr,
+                     unsigned long long *key)
+{
+    extern __shared__ __align__(16) unsigned char fb_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int D0 = net.dims[0], maxw = net.maxw;
+    float *s_lo = reinterpret_cast<float *>(fb_smem) + (size_t)warp * 4 * maxw;     // [2][maxw]
+    float *s_hi = s_lo + 2 * maxw;
+    const bool relaxed = ra_col >= 0;
+    for (int64_t p = (int64_t)blockIdx.x * FB_BOX_WARPS + warp; p < n; p += (int64_t)gridDim.x * FB_BOX_WARPS) {
+        if (key[p] == FB_SCREEN_NOSEARCH) continue;
+        const int32_t *box = boxes + p * (2 * D0);
+        const uint32_t W = (uint32_t)(__ldg(box + 2 * pa_col + 1) - __ldg(box + 2 * pa_col) + 1);
+        if (W == 0 || W > (relaxed ? FB_SCREEN_MAX_W_RELAXED : FB_SCREEN_MAX_W_STRICT)) continue;   // the screen kernel flags it
+        bool ok = true;
+        __syncwarp();
+        for (int i = lane; i < D0; i += 32) {
+            int lo = __ldg(box + 2 * i), hi = __ldg(box + 2 * i + 1);
+            if (lo < -(1 << 30) || hi > (1 << 30) || lo > hi) ok = false;
+            else if (relaxed && i == ra_col) { lo -= ra_thr; hi += ra_thr; }
+            s_lo[i] = (float)lo; s_hi[i] = (float)hi;
+        }
+        if (!__all_sync(0xffffffffu, ok)) continue;
+        __syncwarp();
+        for (int l = 0; l < net.L; ++l) {
+            const int IN = net.dims[l], OUT = net.dims[l + 1];
+            const bool last = (l == net.L - 1);
+            const float *ilo = s_lo + (l & 1) * maxw, *ihi = s_hi + (l & 1) * maxw;
+            float *olo = s_lo + ((l + 1) & 1) * maxw, *ohi = s_hi + ((l + 1) & 1) * maxw;
+            const float *Wl = net.W32 + net.woff[l];
+            for (int j = lane; j < OUT; j += 32) {
+                float lo = 0.0f, hi = 0.0f;
+                for (int k = 0; k < IN; ++k) {
+                    const float w = __ldg(Wl + (size_t)k * OUT + j);
+                    const bool neg = w < 0.0f;
+                    const float xl = ilo[k], xh = ihi[k];
+                    lo = __fmaf_rn(w, neg ? xh : xl, lo);
+                    hi = __fmaf_rn(w, neg ? xl : xh, hi);
+                }
+                const float bj = __ldg(net.B32 + net.boff[l] + j);
+                lo = __fadd_rn(lo, bj); hi = __fadd_rn(hi, bj);
+                olo[j] = (last || fb_pos(lo)) ? lo : 0.0f;
+                ohi[j] = (last || fb_pos(hi)) ? hi : 0.0f;
+            }
+            __syncwarp();
+        }
+        if (lane == 0) {
+            const float ylo = s_lo[(net.L & 1) * maxw], yhi = s_hi[(net.L & 1) * maxw];
+            if (ylo > 0.0f || yhi < 0.0f) key[p] = FB_SCREEN_NOSEARCH;
+        }
+    }
+}
+
 extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_t *boxes, const int32_t *samples, int S,
                                       uint64_t seed, int64_t first_index, int pa_col, int ra_col, int ra_threshold,
                                       int32_t *ce_sample, int32_t *pa_pos, int32_t *pa_neg, int32_t *ra_dpos, int32_t *ra_dneg,
@@ -967,6 +1028,14 @@ extern "C" int fb_partition_screen_ex(const fb_model *m, int64_t n, const int32_
         FB_CUDA(cudaMemsetAsync(key.p, 0xff, sizeof(unsigned long long) * n, st));
     }
     const bool spec_screen = fb_use_spec(m) && (ra_col < 0 || m->gen.P <= FB_SCREEN_SPEC_RELAXED_MAXP);
+    if (samples == nullptr && !(spec_screen && m->gen.P <= FB_SCREEN_SPEC_RELAXED_MAXP) && m->gen.maxw <= FB_MAXW) {
+        // (the small specialised kernels run this pass themselves, per warp)
+        const size_t bsmem = sizeof(float) * FB_BOX_WARPS * 4 * m->gen.maxw;
+        const int bgrid = (int)std::min<int64_t>((n + FB_BOX_WARPS - 1) / FB_BOX_WARPS, (int64_t)m->num_sms * 8);
+        fb_screen_box_kernel<<<bgrid, FB_BOX_WARPS * 32, bsmem, st>>>(m->gen, n, boxes, pa_col, ra_col, ra_threshold,
+                                                                      (unsigned long long *)key.p);
+        FB_CUDA(cudaGetLastError());
+    }
     if (spec_screen) {
         FB_CUDA(m->spec->partition_screen(m->p32, samples == nullptr, n, boxes, samples, seed, first_index, S, chunks,
                                           chunk_len, pa_col, ra_col, ra_threshold, (unsigned long long *)key.p, m->num_sms, st));

@@ -215,7 +215,9 @@ __device__ __forceinline__ VecD<K> fb_add(const VecD<K> &a, double b)
 
 // Specialised architectures above this many weights: relaxed partition screens run on the tiled runtime-shape kernel and
 // the strict ones carry no interval pass (the fully unrolled interval forward takes minutes per kernel to compile)
+#ifndef FB_SCREEN_SPEC_RELAXED_MAXP
 #define FB_SCREEN_SPEC_RELAXED_MAXP 1500
+#endif
 
 // verdict byte
 #define FB_VERDICT_CERTIFIED 1u     // output logit provably one-signed over the box (outward-rounded enclosure)
