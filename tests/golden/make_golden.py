@@ -565,6 +565,59 @@ def relaxed_case():
     print("relaxed case:", len(ok), "pairs,", int(np.sum(ok)), "admissible")
 
 
+def counterexample_cases():
+    """Known answers shipped with the reference: experimentData/task5/AC/counterexamples-fairify-AC-{1,2,3}.csv, the decoded
+    counterexample pairs its drivers wrote (src/AC/Verify-AC-experiment-new.py:344-399) with `output` = sigmoid(net(x)) of
+    the float32-cast point and `prediction` = its class.  The rows are re-encoded with the encoders load_adult_ac1 fits
+    (utils/verif_utils.py:133-171: LabelEncoder per categorical column, 20 uniform bins for capital-gain / -loss, decoded
+    as the bin's integer midpoint) on data/adult/adult.{data,test}:
+    python tests/golden/make_golden.py counterexamples  ->  tests/golden/counterexamples.npz"""
+    from sklearn.preprocessing import KBinsDiscretizer, LabelEncoder
+    cols = ['age', 'workclass', 'fnlwgt', 'education', 'education-num', 'marital-status', 'occupation', 'relationship',
+            'race', 'sex', 'capital-gain', 'capital-loss', 'hours-per-week', 'native-country', 'income-per-year']
+    train = pd.read_csv(os.path.join(REF, "data", "adult", "adult.data"), header=None, names=cols, skipinitialspace=True, na_values=['?'])
+    test = pd.read_csv(os.path.join(REF, "data", "adult", "adult.test"), header=0, names=cols, skipinitialspace=True, na_values=['?'])
+    df = pd.concat([test, train], ignore_index=True).drop(columns=['fnlwgt']).dropna()
+    enc = {}
+    for f in ['sex', 'workclass', 'education', 'marital-status', 'occupation', 'relationship', 'native-country', 'race']:
+        enc[f] = LabelEncoder().fit(df[f])
+    for f in ['capital-gain', 'capital-loss']:
+        enc[f] = KBinsDiscretizer(n_bins=20, encode='ordinal', strategy='uniform').fit(df[[f]])
+    D = domains.DOMAINS["AC"]
+    weights = np.load(os.path.join(HERE, "weights.npz"))
+    out = {}
+    for name in ("AC-1", "AC-2", "AC-3"):
+        c = pd.read_csv(os.path.join(REF, "experimentData", "task5", "AC", f"counterexamples-fairify-{name}.csv"))
+        X = []
+        for _, r in c.iterrows():
+            x = []
+            for f in D.columns:
+                if isinstance(enc.get(f), LabelEncoder):
+                    x.append(int(enc[f].transform([r[f]])[0]))
+                elif f in enc:
+                    e = enc[f].bin_edges_[0]
+                    x.append([int((e[k] + e[k + 1]) / 2) for k in range(len(e) - 1)].index(int(r[f])))
+                else:
+                    x.append(int(r[f]))
+            X.append(x)
+        X = np.array(X, dtype=np.int64)
+        # the re-encoding is right if the reference's own arithmetic (float32 weights on the float32-cast point) gives the column back
+        L = int(weights[f"{name}/L"])
+        a = X.astype(np.float32)
+        for l in range(L):
+            a = a @ weights[f"{name}/w{l}"] + weights[f"{name}/b{l}"]
+            if l < L - 1:
+                a = np.maximum(a, np.float32(0))
+        got = 1.0 / (1.0 + np.exp(-a[:, 0].astype(np.float64)))
+        assert np.allclose(got, c["output"].to_numpy(), rtol=0, atol=5e-6), name
+        assert np.array_equal((got > 0.5).astype(int), c["prediction"].to_numpy()), name
+        lo = np.array([D.ranges[f][0] for f in D.columns]); hi = np.array([D.ranges[f][1] for f in D.columns])
+        assert np.all((X >= lo) & (X <= hi)), name
+        out[f"{name}/x"] = X; out[f"{name}/output"] = c["output"].to_numpy(); out[f"{name}/prediction"] = c["prediction"].to_numpy().astype(np.uint8)
+        print(name, len(X), "rows, max |sigmoid - output|", np.abs(got - c["output"].to_numpy()).max())
+    np.savez_compressed(os.path.join(HERE, "counterexamples.npz"), **out)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "hybrid":
         hybrid_case()
@@ -574,5 +627,7 @@ if __name__ == "__main__":
         sliver_case()
     elif len(sys.argv) > 1 and sys.argv[1] == "relaxed":
         relaxed_case()
+    elif len(sys.argv) > 1 and sys.argv[1] == "counterexamples":
+        counterexample_cases()
     else:
         main()

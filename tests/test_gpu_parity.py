@@ -584,6 +584,28 @@ def test_relaxed_screen_edge_cases(eng, name):
     assert all(t.numel() == 0 for t in empty)
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-2", "AC-3"])
+def test_reference_counterexample_csvs_on_the_device(eng, name):
+    """The reference's shipped counterexample pairs (tests/golden/counterexamples.npz, see test_oracle_golden.py): device
+    logits in float32 and float64 reproduce the printed sigmoid outputs and classes, and the strict partition screen finds
+    a pair in the degenerate box of each first point (protected column over its range)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "counterexamples.npz"))
+    w, b = G.wb(name)
+    m = eng.Model(w, b); dom = G.domain(name)
+    X = z[f"{name}/x"]
+    y32 = m.forward(X.astype(np.float32)).cpu().numpy().astype(np.float64)
+    y64 = m.forward(X.astype(np.float64)).cpu().numpy()
+    assert np.allclose(1.0 / (1.0 + np.exp(-y32)), z[f"{name}/output"], rtol=0, atol=5e-6)
+    assert np.array_equal((y32 > 0).astype(np.uint8), z[f"{name}/prediction"])
+    assert np.array_equal((y64 > 0).astype(np.uint8), z[f"{name}/prediction"])
+    pa = dom.columns.index("sex")
+    first = X[0::2]
+    boxes = np.stack([first, first], axis=2).astype(np.int32)
+    boxes[:, pa, 0], boxes[:, pa, 1] = dom.ranges["sex"]
+    ce, vp, vn = [t.cpu().numpy() for t in m.partition_screen(boxes, pa, S=4, seed=1)]
+    assert np.all(ce == 0) and np.all(vp != vn)                     # every sample of such a box is the point itself
+
+
 def test_partition_screen_rejects_what_it_cannot_encode(eng):
     """A protected range wider than the key's fields is skipped and flagged, not silently mis-encoded; argument checks."""
     w, b = G.wb("GC-1")

@@ -296,6 +296,25 @@ def test_hybrid_predict_matches_reference_functions():
     assert np.array_equal(logit > 0, z["pred"] > 0.5)
 
 
+@pytest.mark.parametrize("name", ["AC-1", "AC-2", "AC-3"])
+def test_reference_counterexample_csvs_are_reproduced(name):
+    """Known answers shipped with the reference (experimentData/task5/AC/counterexamples-fairify-AC-*.csv, re-encoded by
+    make_golden.py counterexamples): `output` = sigmoid(net(x)) of the float32-cast point as the reference's driver
+    printed it (float32 arithmetic, pruned network), `prediction` = its class; consecutive rows are a counterexample pair."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "counterexamples.npz"))
+    net = O.Net(*G.wb(name))
+    X = z[f"{name}/x"]
+    y = O.forward_f32(net, X.astype(np.float32)).astype(np.float64)
+    assert np.allclose(1.0 / (1.0 + np.exp(-y)), z[f"{name}/output"], rtol=0, atol=5e-6)
+    assert np.array_equal((y > 0).astype(np.uint8), z[f"{name}/prediction"])
+    y64 = O.forward_f64(net, X.astype(np.float64))
+    assert np.array_equal((y64 > 0).astype(np.uint8), z[f"{name}/prediction"])
+    pred = z[f"{name}/prediction"]
+    assert np.all(pred[0::2] != pred[1::2])                               # every pair flips the class
+    diff = X[0::2] != X[1::2]
+    assert np.all(diff.sum(axis=1) == 1) and np.all(diff[:, G.domain(name).columns.index("sex")])   # in the protected column only
+
+
 def test_relaxed_pairs_are_the_ones_the_reference_property_admits():
     """tests/golden/relaxed_case.npz: 720 concrete pairs judged by the property relaxed/AC/Verify-AC.py:122-132 builds
     with the reference's own in_const_adult / in_const_diff_adult / in_const_domain_adult (Z3, make_golden.py relaxed).
